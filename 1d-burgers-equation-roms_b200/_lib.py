@@ -1,0 +1,65 @@
+"""ctypes binding of libburgers_b200.so (include/burgers_b200.h).  No fallback: if the library is
+missing or a call fails this raises — the product never computes on the CPU."""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import c_char_p, c_double, c_int, c_longlong, c_void_p
+
+PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(PKG_DIR, "libburgers_b200.so")
+
+BX_OK, BX_ERR_INVALID, BX_ERR_CUDA, BX_ERR_UNSUPPORTED, BX_ERR_PROJECTION = 0, -1, -2, -3, -4
+BX_GALERKIN, BX_LSPG = 0, 1
+
+P = c_void_p  # device pointer / stream
+
+SIGNATURES = {
+    "bx_version": (c_int, []),
+    "bx_last_error": (c_char_p, []),
+    "bx_device_sm_count": (c_int, []),
+    "bx_mass_bands": (c_int, [c_int, P, P, P, P, P]),
+    "bx_diffusion_bands": (c_int, [c_int, P, P, P, P, P]),
+    "bx_convection_bands": (c_int, [c_int, c_int, P, P, P, P, P, P]),
+    "bx_convection_derivative_bands": (c_int, [c_int, P, P, P, P, P]),
+    "bx_forcing_vector": (c_int, [c_int, c_int, P, P, P, P]),
+    "bx_supg_term": (c_int, [c_int, c_int, P, P, P, P, P]),
+    "bx_assemble_picard": (c_int, [c_int, c_int, P, P, P, P, P, c_double, c_double, c_int, P, P, P, P, P, P]),
+    "bx_tridiag_solve_update": (c_int, [c_int, c_int, P, P, P, P, P, P, P, P]),
+    "bx_workspace_bytes": (c_longlong, []),
+    "bx_fom_picard_trajectories": (c_int, [c_int, c_int, c_int, P, P, c_int, P, P, c_double, c_double,
+                                           c_double, c_int, P, P, P, P]),
+}
+
+_lib = None
+
+
+class BurgersB200Error(RuntimeError):
+    """A C-ABI call returned a negative code (native precedent: std::runtime_error ->
+    RuntimeError, PybindExample/sparse_solver_parallel.cpp:13-25)."""
+
+
+def load():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a).  There is no CPU fallback.")
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the library does not export a declared symbol
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(code: int, what: str):
+    if code == BX_OK:
+        return
+    msg = load().bx_last_error().decode("utf-8", "replace")
+    if code == BX_ERR_PROJECTION:
+        raise ValueError(msg)
+    raise BurgersB200Error(f"{what} failed with code {code}: {msg}")

@@ -1,0 +1,242 @@
+"""Host-side mirror of the reference's `FEMBurgers` (FEM/fem_burgers.py:314-1574) for the hot
+path: same constructor, method names, argument order/meaning, return types and error
+behaviour; every number is produced by the sm_100a kernels behind include/burgers_b200.h.
+
+Legacy single-sample methods take/return numpy (and scipy.sparse CSC for the matrices, as the
+reference does) and synchronise before returning.  The `*_batch` / `*_bands` methods are the new
+batched surface: torch CUDA tensors in and out, asynchronous on the current CUDA stream.
+
+PyTorch is used for device memory, streams and (in sweep.py) torch.distributed only.
+There is no CPU path: without a CUDA device or without the built library these raise.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import _lib
+
+
+def _require_cuda():
+    if not torch.cuda.is_available():
+        raise RuntimeError("burgers_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def validate_mesh(X, T):
+    """The kernels assume the reference's structured connectivity T[e] = (e+1, e+2), 1-based
+    (FEM/fom.py:16, element_nodes = T[elem,:] - 1 at FEM/fem_burgers.py:330)."""
+    X = np.ascontiguousarray(np.asarray(X, dtype=np.float64))
+    if X.ndim != 1 or X.size < 2:
+        raise ValueError("X must be a 1-D array of at least 2 node coordinates")
+    if not np.all(np.diff(X) > 0):
+        raise ValueError("X must be strictly increasing")
+    if T is not None:
+        T = np.asarray(T)
+        m = X.size - 1
+        ok = T.shape == (m, 2) and np.array_equal(T[:, 0], np.arange(1, m + 1)) and \
+            np.array_equal(T[:, 1], np.arange(2, m + 2))
+        if not ok:
+            raise ValueError("only the structured 2-node connectivity T[e] = (e+1, e+2) (1-based) is supported")
+    return X
+
+
+class FEMBurgers:
+    def __init__(self, X, T=None, device=None):
+        self.X = validate_mesh(X, T)
+        self.T = T if T is not None else np.array([np.arange(1, self.X.size), np.arange(2, self.X.size + 1)]).T
+        # quadrature data kept as attributes for callers that read them (FEM/fem_burgers.py:318-322)
+        self.ngaus = 2
+        self.zgp = np.array([-np.sqrt(3) / 3, np.sqrt(3) / 3])
+        self.wgp = np.array([1, 1])
+        self.N = np.array([(1 - self.zgp) / 2, (1 + self.zgp) / 2]).T
+        self.Nxi = np.array([[-1 / 2, 1 / 2], [-1 / 2, 1 / 2]])
+        self.n_nodes = int(self.X.size)
+        self._device = device
+        self._Xd = None
+        self._ws = None
+        self.last_iters = None  # per-step nonlinear iteration counts of the last legacy call
+
+    # ------------------------------------------------------------------ device plumbing
+    @property
+    def device(self):
+        if self._device is None:
+            _require_cuda()
+            self._device = torch.device("cuda", torch.cuda.current_device())
+        return torch.device(self._device)
+
+    @property
+    def Xd(self):
+        if self._Xd is None:
+            _require_cuda()
+            self._Xd = torch.from_numpy(self.X).to(self.device)
+        return self._Xd
+
+    def _workspace(self):
+        if self._ws is None:
+            self._ws = torch.zeros(int(_lib.load().bx_workspace_bytes()), dtype=torch.uint8, device=self.device)
+        return self._ws
+
+    def _dev(self, a, shape=None):
+        """numpy / scalar / tensor -> contiguous float64 CUDA tensor."""
+        if isinstance(a, torch.Tensor):
+            t = a.to(device=self.device, dtype=torch.float64)
+        else:
+            t = torch.from_numpy(np.ascontiguousarray(np.asarray(a, dtype=np.float64))).to(self.device)
+        if shape is not None:
+            t = t.reshape(shape)
+        return t.contiguous()
+
+    def _new(self, *shape, dtype=torch.float64):
+        return torch.empty(shape, dtype=dtype, device=self.device)
+
+    # ------------------------------------------------------------------ batched operators
+    def mass_bands(self):
+        """(dl, d, du) of M, each (N,) — compute_mass_matrix, FEM/fem_burgers.py:324."""
+        N = self.n_nodes
+        dl, d, du = self._new(N), self._new(N), self._new(N)
+        lib = _lib.load()
+        _lib.check(lib.bx_mass_bands(N, _ptr(self.Xd), _ptr(dl), _ptr(d), _ptr(du), _stream()), "bx_mass_bands")
+        return dl, d, du
+
+    def diffusion_bands(self):
+        N = self.n_nodes
+        dl, d, du = self._new(N), self._new(N), self._new(N)
+        lib = _lib.load()
+        _lib.check(lib.bx_diffusion_bands(N, _ptr(self.Xd), _ptr(dl), _ptr(d), _ptr(du), _stream()),
+                   "bx_diffusion_bands")
+        return dl, d, du
+
+    def convection_bands(self, U):
+        """U (B, N) -> (dl, d, du) each (B, N) — compute_convection_matrix, :389."""
+        U = self._dev(U).reshape(-1, self.n_nodes)
+        B, N = U.shape
+        dl, d, du = self._new(B, N), self._new(B, N), self._new(B, N)
+        lib = _lib.load()
+        _lib.check(lib.bx_convection_bands(B, N, _ptr(self.Xd), _ptr(U), _ptr(dl), _ptr(d), _ptr(du), _stream()),
+                   "bx_convection_bands")
+        return dl, d, du
+
+    def convection_derivative_bands(self):
+        N = self.n_nodes
+        dl, d, du = self._new(N), self._new(N), self._new(N)
+        lib = _lib.load()
+        _lib.check(lib.bx_convection_derivative_bands(N, _ptr(self.Xd), _ptr(dl), _ptr(d), _ptr(du), _stream()),
+                   "bx_convection_derivative_bands")
+        return dl, d, du
+
+    def forcing_vector_batch(self, mu2):
+        mu2 = self._dev(mu2).reshape(-1)
+        B, N = mu2.numel(), self.n_nodes
+        F = self._new(B, N)
+        lib = _lib.load()
+        _lib.check(lib.bx_forcing_vector(B, N, _ptr(self.Xd), _ptr(mu2), _ptr(F), _stream()), "bx_forcing_vector")
+        return F
+
+    def supg_term_batch(self, U, mu2):
+        U = self._dev(U).reshape(-1, self.n_nodes)
+        mu2 = self._dev(mu2).reshape(-1)
+        B, N = U.shape
+        if mu2.numel() != B:
+            raise ValueError("mu2 must have one entry per state")
+        S = self._new(B, N)
+        lib = _lib.load()
+        _lib.check(lib.bx_supg_term(B, N, _ptr(self.Xd), _ptr(U), _ptr(mu2), _ptr(S), _stream()), "bx_supg_term")
+        return S
+
+    def assemble_picard(self, Uk, Un, mu1, mu2, At, E=0.0, supg=True, want_b=True):
+        """One Picard linearisation for B states (FEM/fem_burgers.py:667-689).
+        Returns dl, d, du, b, R — all (B, N) CUDA tensors (b is None when want_b=False)."""
+        Uk = self._dev(Uk).reshape(-1, self.n_nodes)
+        Un = self._dev(Un).reshape(-1, self.n_nodes)
+        B, N = Uk.shape
+        mu1 = self._dev(mu1).reshape(-1)
+        mu2 = self._dev(mu2).reshape(-1)
+        if Un.shape != Uk.shape or mu1.numel() != B or mu2.numel() != B:
+            raise ValueError("Uk, Un, mu1, mu2 batch sizes differ")
+        dl, d, du, R = self._new(B, N), self._new(B, N), self._new(B, N), self._new(B, N)
+        b = self._new(B, N) if want_b else None
+        lib = _lib.load()
+        _lib.check(lib.bx_assemble_picard(B, N, _ptr(self.Xd), _ptr(Uk), _ptr(Un), _ptr(mu1), _ptr(mu2),
+                                          float(At), float(E), int(bool(supg)), _ptr(dl), _ptr(d), _ptr(du),
+                                          _ptr(b), _ptr(R), _stream()), "bx_assemble_picard")
+        return dl, d, du, b, R
+
+    def tridiag_solve_update(self, dl, d, du, R, Uk, out=None):
+        """delta = A^-1(-R); U1 = Uk + delta; err = |delta|/|U1| (FEM/fem_burgers.py:692-698)."""
+        Uk = self._dev(Uk).reshape(-1, self.n_nodes)
+        B, N = Uk.shape
+        U1 = out if out is not None else self._new(B, N)
+        err = self._new(B)
+        lib = _lib.load()
+        _lib.check(lib.bx_tridiag_solve_update(B, N, _ptr(dl), _ptr(d), _ptr(du), _ptr(R), _ptr(Uk), _ptr(U1),
+                                               _ptr(err), _stream()), "bx_tridiag_solve_update")
+        return U1, err
+
+    # ------------------------------------------------------------------ batched trajectories
+    def fom_burgers_batch(self, At, nTimeSteps, u0, mu1, E, mu2, out=None, iters_out=None,
+                          tol=1e-6, kmax=20):
+        """fom_burgers (FEM/fem_burgers.py:646) for B samples: mu1, mu2 (B,).
+        Returns U (B, nTimeSteps+1, N) and iters (B, nTimeSteps) int32, CUDA tensors."""
+        mu1 = self._dev(mu1).reshape(-1)
+        mu2 = self._dev(mu2).reshape(-1)
+        B, N = mu1.numel(), self.n_nodes
+        if mu2.numel() != B:
+            raise ValueError("mu1 and mu2 must have the same number of samples")
+        u0 = self._dev(u0)
+        if u0.numel() == N:
+            batched = 0
+        elif u0.numel() == B * N:
+            batched = 1
+        else:
+            raise ValueError("u0 must have shape (N,) or (B, N)")
+        nT = int(nTimeSteps)
+        U = out if out is not None else self._new(B, nT + 1, N)
+        if tuple(U.shape) != (B, nT + 1, N) or U.dtype != torch.float64 or not U.is_contiguous():
+            raise ValueError("out must be a contiguous float64 tensor of shape (B, nTimeSteps+1, N)")
+        iters = iters_out if iters_out is not None else self._new(B, nT, dtype=torch.int32)
+        lib = _lib.load()
+        _lib.check(lib.bx_fom_picard_trajectories(B, N, nT, _ptr(self.Xd), _ptr(u0), batched, _ptr(mu1),
+                                                  _ptr(mu2), float(At), float(E), float(tol), int(kmax),
+                                                  _ptr(U), _ptr(iters), _ptr(self._workspace()), _stream()),
+                   "bx_fom_picard_trajectories")
+        return U, iters
+
+    # ------------------------------------------------------------------ legacy surface (numpy / scipy in-out)
+    def _csc(self, bands):
+        import scipy.sparse as sp  # return type of the reference (:353); not used for any arithmetic here
+        dl, d, du = (t.reshape(-1).cpu().numpy() for t in bands)
+        return sp.diags([dl[1:], d, du[:-1]], [-1, 0, 1], format="csc")
+
+    def compute_mass_matrix(self):
+        return self._csc(self.mass_bands())
+
+    def compute_diffusion_matrix(self):
+        return self._csc(self.diffusion_bands())
+
+    def compute_convection_matrix(self, U_n):
+        return self._csc(self.convection_bands(np.asarray(U_n, dtype=np.float64).reshape(1, -1)))
+
+    def compute_convection_matrix_derivative(self, U_n):
+        return self._csc(self.convection_derivative_bands())
+
+    def compute_forcing_vector(self, mu2):
+        return self.forcing_vector_batch([float(mu2)]).reshape(-1).cpu().numpy()
+
+    def compute_supg_term(self, U_n, mu2):
+        return self.supg_term_batch(np.asarray(U_n, dtype=np.float64).reshape(1, -1), [float(mu2)]) \
+            .reshape(-1).cpu().numpy()
+
+    def fom_burgers(self, At, nTimeSteps, u0, mu1, E, mu2):
+        """Drop-in for FEMBurgers.fom_burgers: returns ndarray (N, nTimeSteps+1)."""
+        U, it = self.fom_burgers_batch(At, nTimeSteps, np.asarray(u0, dtype=np.float64), [float(mu1)], E,
+                                       [float(mu2)])
+        self.last_iters = it[0].cpu().numpy()
+        return np.ascontiguousarray(U[0].cpu().numpy().T)

@@ -1,0 +1,95 @@
+/*
+ * burgers_b200.h — C ABI of libburgers_b200.so (sm_100a).
+ *
+ * Drop-in boundary for ONE hot path of SADPR/1D-Burgers-Equation-ROMs: the implicit
+ * linear-FEM time stepping of the 1D inviscid Burgers FOM over many (mu1, mu2) samples and
+ * the POD Galerkin/LSPG (and quadratic-manifold) PROM step that reuses the same operators.
+ * Each entry point cites the reference interface (file:line under the reference root) it
+ * replaces.  INTEGRATION.md shows the ctypes binding a maintainer of the reference adds.
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes; no torch / C++ types.
+ *   - every pointer is a DEVICE pointer (FP64 unless stated) owned by the caller; nothing is
+ *     allocated, freed or synchronised inside; work is enqueued on `stream`
+ *     (a cudaStream_t passed as void*, NULL = legacy default stream).
+ *   - return value: BX_OK (0) or a negative BX_ERR_* code; bx_last_error() gives the text.
+ *   - "bands" of a tridiagonal N x N matrix are three length-N arrays dl (sub-diagonal,
+ *     dl[0] unused = 0), d (diagonal), du (super-diagonal, du[N-1] unused = 0).  Batched
+ *     arrays are sample-major: element (b, i) at [b*N + i].
+ *   - the mesh is the reference's structured 2-node mesh T[e] = (e+1, e+2)
+ *     (FEM/fom.py:16); X (N nodes, strictly increasing, possibly non-uniform) is the only
+ *     mesh input.
+ *   - trajectories are written as U[b][step][node], (B, nsteps+1, N); the reference's
+ *     per-sample layout (N, nsteps+1) (FEM/fem_burgers.py:650) is its transpose.
+ *   - iteration counts: iters[b][step], int32, the number of nonlinear iterations the
+ *     reference's while-loop would have executed for that step.
+ */
+#ifndef BURGERS_B200_H
+#define BURGERS_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BX_OK                0
+#define BX_ERR_INVALID      -1   /* bad argument (size, null pointer, unsupported N)     */
+#define BX_ERR_CUDA         -2   /* a CUDA runtime call / launch failed                  */
+#define BX_ERR_UNSUPPORTED  -3   /* configuration outside what the kernels cover         */
+#define BX_ERR_PROJECTION   -4   /* projection is not BX_GALERKIN / BX_LSPG
+                                    (reference: ValueError, FEM/fem_burgers.py:764,1158)  */
+
+#define BX_GALERKIN 0
+#define BX_LSPG     1
+
+int         bx_version(void);
+const char *bx_last_error(void);
+/* number of SMs / device name of the current device (diagnostics for bench.py) */
+int         bx_device_sm_count(void);
+
+/* ---- L1 operators -------------------------------------------------------------------- */
+/* FEMBurgers.compute_mass_matrix, FEM/fem_burgers.py:324-353 */
+int bx_mass_bands(int N, const double *X, double *dl, double *d, double *du, void *stream);
+/* FEMBurgers.compute_diffusion_matrix, FEM/fem_burgers.py:355-387 */
+int bx_diffusion_bands(int N, const double *X, double *dl, double *d, double *du, void *stream);
+/* FEMBurgers.compute_convection_matrix(U_n), FEM/fem_burgers.py:389-425 ; U (B, N) */
+int bx_convection_bands(int B, int N, const double *X, const double *U,
+                        double *dl, double *d, double *du, void *stream);
+/* FEMBurgers.compute_convection_matrix_derivative(U_n), FEM/fem_burgers.py:463-498 */
+int bx_convection_derivative_bands(int N, const double *X, double *dl, double *d, double *du,
+                                   void *stream);
+/* FEMBurgers.compute_forcing_vector(mu2), FEM/fem_burgers.py:427-461 ; mu2 (B,), F (B, N) */
+int bx_forcing_vector(int B, int N, const double *X, const double *mu2, double *F, void *stream);
+/* FEMBurgers.compute_supg_term(U_n, mu2), FEM/fem_burgers.py:500-581 ; S (B, N) */
+int bx_supg_term(int B, int N, const double *X, const double *U, const double *mu2, double *S,
+                 void *stream);
+
+/* ---- one Picard linearisation, bands materialised in HBM ----------------------------- */
+/* FEM/fem_burgers.py:667-689 (= :730-752): A = M + At C(Uk) + At E K, row 0 <- e0^T;
+ * b = M Un + At F(mu2) - At S(Uk, mu2) (S dropped when supg == 0, as :1141), b[0] = mu1;
+ * R = A Uk - b.  Writes dl, d, du, R (and b when b != NULL), all (B, N).                */
+int bx_assemble_picard(int B, int N, const double *X, const double *Uk, const double *Un,
+                       const double *mu1, const double *mu2, double At, double E, int supg,
+                       double *dl, double *d, double *du, double *b, double *R, void *stream);
+/* FEM/fem_burgers.py:692-698: delta = A^-1 (-R); Uk1 = Uk + delta;
+ * err[b] = |delta|_2 / |Uk1|_2.  One warp per system; N <= 1024.  Uk1 may alias Uk.      */
+int bx_tridiag_solve_update(int B, int N, const double *dl, const double *d, const double *du,
+                            const double *R, const double *Uk, double *Uk1, double *err,
+                            void *stream);
+
+/* ---- whole trajectories (the sweep of FEM/paper_training_stage.py:28-53) ------------- */
+/* bytes of zero-initialisable scratch the trajectory kernels need (work-queue counters). */
+long long bx_workspace_bytes(void);
+
+/* FEMBurgers.fom_burgers, FEM/fem_burgers.py:646-707, for B samples at once.
+ * u0: (N,) shared by all samples when u0_batched == 0, else (B, N).
+ * tol, kmax: the literals 1e-6 / 20 of :663.  U: (B, nsteps+1, N).  iters: (B, nsteps) or NULL.
+ * workspace: bx_workspace_bytes() bytes (contents ignored, overwritten).                  */
+int bx_fom_picard_trajectories(int B, int N, int nsteps, const double *X, const double *u0,
+                               int u0_batched, const double *mu1, const double *mu2,
+                               double At, double E, double tol, int kmax,
+                               double *U, int *iters, void *workspace, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BURGERS_B200_H */

@@ -1,0 +1,73 @@
+"""CPU: the C-ABI library builds, loads, and exports every symbol include/burgers_b200.h declares;
+host-side argument validation that needs no GPU."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    import burgers_b200
+    burgers_b200.build_library()
+    return burgers_b200._lib.load()
+
+
+def declared_symbols():
+    src = open(os.path.join(ROOT, "include", "burgers_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(bx_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_header_symbols_exported(lib):
+    import burgers_b200
+    raw = ctypes.CDLL(burgers_b200.LIB_PATH)
+    names = declared_symbols()
+    assert len(names) >= 13
+    for n in names:
+        assert hasattr(raw, n), f"{n} declared in include/burgers_b200.h but not exported"
+    # and every declared symbol has a ctypes signature in the host binding
+    assert set(names) == set(burgers_b200._lib.SIGNATURES)
+
+
+def test_version_and_workspace(lib):
+    assert lib.bx_version() >= 100
+    assert lib.bx_workspace_bytes() >= 4
+
+
+def test_argument_validation_without_gpu(lib):
+    # invalid sizes are rejected before any CUDA call is made
+    assert lib.bx_fom_picard_trajectories(4, 1, 10, None, None, 0, None, None, 0.05, 0.0, 1e-6, 20,
+                                          None, None, None, None) == -1
+    assert b"2 nodes" in lib.bx_last_error()
+    assert lib.bx_fom_picard_trajectories(4, 512, 10, None, None, 0, None, None, 0.05, 0.0, 1e-6, 0,
+                                          None, None, None, None) == -1
+    assert lib.bx_tridiag_solve_update(1, 4096, None, None, None, None, None, None, None, None) == -1
+    assert lib.bx_mass_bands(1, None, None, None, None, None) == -1
+
+
+def test_mesh_validation():
+    import burgers_b200
+    X = np.linspace(0, 100, 16)
+    T = np.array([np.arange(1, 16), np.arange(2, 17)]).T
+    burgers_b200.validate_mesh(X, T)
+    with pytest.raises(ValueError):
+        burgers_b200.validate_mesh(X, T[::-1])
+    with pytest.raises(ValueError):
+        burgers_b200.validate_mesh(X[::-1], T)
+    with pytest.raises(ValueError):
+        burgers_b200.validate_mesh(X, T - 1)   # 0-based connectivity is not the reference's convention
+
+
+def test_no_cpu_fallback():
+    import torch
+    import burgers_b200
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    fem = burgers_b200.FEMBurgers(np.linspace(0, 100, 64))
+    with pytest.raises(RuntimeError):
+        fem.fom_burgers(0.05, 2, np.ones(64), 4.75, 0.0, 0.02)

@@ -1,0 +1,109 @@
+"""GPU parity of the fused FOM trajectory kernel (through the C ABI) against the oracle, the
+reference-run golden vectors and the reference's stored fixtures.
+Tolerance (north_star): per-time-step relative L2 <= 1e-10 in FP64, identical iteration counts."""
+import numpy as np
+import pytest
+
+from conftest import rel_l2_per_step
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-10
+
+
+@pytest.fixture(scope="module")
+def fem512(oracle):
+    import burgers_b200
+    X, T = oracle.mesh(512)
+    return burgers_b200.FEMBurgers(X, T)
+
+
+@pytest.mark.parametrize("key", ["4.75_0.02", "4.25_0.015", "6.2_0.04"])
+def test_legacy_fom_vs_reference_run(key, golden, fem512):
+    g = golden("fom_short.npz")
+    mu1, mu2 = map(float, key.split("_"))
+    U = fem512.fom_burgers(0.05, 12, np.ones(512), mu1, 0.0, mu2)
+    assert U.shape == (512, 13) and U.dtype == np.float64
+    assert np.array_equal(fem512.last_iters, g["it_" + key])
+    assert rel_l2_per_step(U, g["U_" + key]) <= TOL
+
+
+def test_nonuniform_mesh_diffusion_and_small_n(golden):
+    import burgers_b200
+    g = golden("fom_short.npz")
+    X = g["nonuni_X"]; u0 = g["nonuni_u0"]          # N = 37: padded lanes, non-uniform h
+    fem = burgers_b200.FEMBurgers(X)
+    U = fem.fom_burgers(0.02, 8, u0, 2.0, 0.0, 0.04)
+    assert np.array_equal(fem.last_iters, g["nonuni_it"]) and rel_l2_per_step(U, g["nonuni_U"]) <= TOL
+    U = fem.fom_burgers(0.02, 8, u0, 2.0, 0.01, 0.04)    # E != 0
+    assert np.array_equal(fem.last_iters, g["nonuni_E_it"]) and rel_l2_per_step(U, g["nonuni_E_U"]) <= TOL
+    fem = burgers_b200.FEMBurgers(g["n64_X"])
+    U = fem.fom_burgers(0.05, 10, np.ones(64), 4.75, 0.0, 0.02)
+    assert np.array_equal(fem.last_iters, g["n64_it"]) and rel_l2_per_step(U, g["n64_U"]) <= TOL
+
+
+def test_all_14_stored_fixtures_full_500_steps(golden, fem512):
+    """All 14 (mu1, mu2) points the reference ships, 500 steps, in ONE batched launch."""
+    g = golden("fom_fixtures.npz")
+    pts = g["points"]
+    U, it = fem512.fom_burgers_batch(0.05, 500, np.ones(512), pts[:, 0], 0.0, pts[:, 1])
+    U = U.cpu().numpy(); it = it.cpu().numpy()
+    for i in range(14):
+        assert rel_l2_per_step(U[i].T[:, g["steps"]], g[f"U_{i}"]) <= TOL, i
+        assert np.array_equal(it[i], g[f"it_{i}"].astype(np.int32)), i
+
+
+@pytest.mark.parametrize("N", [2, 3, 31, 32, 33, 64, 100, 129, 255, 256, 257, 511, 513, 700, 1024])
+def test_sizes_vs_oracle(N, oracle):
+    import burgers_b200
+    X = np.linspace(0.0, 100.0 * (N - 1) / 511.0, N)
+    fem = burgers_b200.FEMBurgers(X)
+    mu1 = np.array([4.3, 5.1, 4.75]); mu2 = np.array([0.016, 0.029, 0.02])
+    U, it = fem.fom_burgers_batch(0.05, 5, np.ones(N), mu1, 0.0, mu2)
+    Uo, ito = oracle.fom_burgers_batch(X, 0.05, 5, np.ones(N), mu1, 0.0, mu2)
+    assert np.array_equal(it.cpu().numpy(), ito)
+    err = np.max(np.linalg.norm(U.cpu().numpy() - Uo, axis=2) / np.linalg.norm(Uo, axis=2))
+    assert err <= TOL
+
+
+def test_batched_u0_and_ragged_batches(oracle, fem512):
+    X, _ = oracle.mesh(512)
+    rng = np.random.default_rng(5)
+    for B in (1, 5, 33, 130):
+        mu1 = 4.25 + 1.25 * rng.random(B); mu2 = 0.015 + 0.015 * rng.random(B)
+        u0 = 1.0 + 0.1 * rng.random((B, 512))
+        U, it = fem512.fom_burgers_batch(0.05, 3, u0, mu1, 0.0, mu2)
+        for b in range(0, B, max(1, B // 4)):
+            Uo, ito = oracle.fom_burgers(X, 0.05, 3, u0[b], mu1[b], 0.0, mu2[b])
+            assert np.array_equal(it[b].cpu().numpy(), ito)
+            assert rel_l2_per_step(U[b].cpu().numpy().T, Uo) <= TOL
+
+
+def test_empty_batch_and_zero_steps(fem512):
+    U, it = fem512.fom_burgers_batch(0.05, 4, np.ones(512), np.zeros(0), 0.0, np.zeros(0))
+    assert tuple(U.shape) == (0, 5, 512) and tuple(it.shape) == (0, 4)
+    U, it = fem512.fom_burgers_batch(0.05, 0, np.ones(512), [4.75], 0.0, [0.02])
+    assert tuple(U.shape) == (1, 1, 512) and np.array_equal(U[0, 0].cpu().numpy(), np.ones(512))
+
+
+def test_kmax_and_tol_arguments(oracle, fem512):
+    X, _ = oracle.mesh(512)
+    U, it = fem512.fom_burgers_batch(0.05, 4, np.ones(512), [4.75], 0.0, [0.02], tol=1e-3, kmax=7)
+    Uo, ito = oracle.fom_burgers(X, 0.05, 4, np.ones(512), 4.75, 0.0, 0.02, tol=1e-3, kmax=7)
+    assert np.array_equal(it[0].cpu().numpy(), ito)
+    assert rel_l2_per_step(U[0].cpu().numpy().T, Uo) <= TOL
+
+
+def test_config2_slice_properties(oracle, fem512):
+    """Config-2 grid (64 x 64, mu1-major) at full width for a few steps: size-independent
+    properties — Dirichlet node equals mu1 after step 1, iteration counts within [1, 20],
+    and a strided subset equals the oracle."""
+    X, _ = oracle.mesh(512)
+    mu1, mu2 = oracle.parameter_grid(64, 64)
+    U, it = fem512.fom_burgers_batch(0.05, 4, np.ones(512), mu1, 0.0, mu2)
+    Uc = U.cpu().numpy(); itc = it.cpu().numpy()
+    assert np.allclose(Uc[:, 1:, 0], mu1[:, None], rtol=0, atol=1e-12)
+    assert itc.min() >= 1 and itc.max() <= 20 and np.isfinite(Uc).all()
+    sel = np.arange(0, 4096, 257)
+    Uo, ito = oracle.fom_burgers_batch(X, 0.05, 4, np.ones(512), mu1[sel], 0.0, mu2[sel])
+    assert np.array_equal(itc[sel], ito)
+    assert np.max(np.linalg.norm(Uc[sel] - Uo, axis=2) / np.linalg.norm(Uo, axis=2)) <= TOL
