@@ -6,5 +6,6 @@ the root-level shim `burgers_b200` (burgers_b200.py), which registers this packa
 from . import _lib  # noqa: F401
 from .build import build_library, LIB_PATH  # noqa: F401
 from .fem_burgers import FEMBurgers, validate_mesh  # noqa: F401
+from . import sweep  # noqa: F401
 
 __all__ = ["FEMBurgers", "validate_mesh", "build_library", "LIB_PATH"]

@@ -17,6 +17,7 @@
 //   * the only HBM traffic is the 8N-byte snapshot per step (+ 4 B iteration count).
 // Warps pull samples from an atomic work queue (persistent CTAs).
 #include "bx_common.cuh"
+#include <cstdlib>
 
 namespace bx {
 
@@ -40,26 +41,37 @@ struct FomParams {
 template <int M> struct FomSmem {
     static constexpr int EL = (M + 1) * 32;
     static constexpr int NL = M * 32;
-    static constexpr int MESH = 5 * EL + NL;     // off, hc, rh, h6, a6 | dg
-    static constexpr int PER_WARP = EL + 2 * NL; // fsum | AtF, bn
+    static constexpr int MESH = 2 * EL + NL;     // off, h6 | dg
+    static constexpr int PER_WARP = EL + 2 * NL; // hfs | AtF, bn
     static constexpr size_t bytes(int warps) { return sizeof(double) * (MESH + (size_t)warps * PER_WARP); }
 };
 
-template <int M, int WARPS, int MINB>
+// Sum two values over the warp with 7 instead of 10 64-bit shuffles: the two half-warps first
+// trade the value they do not keep, each half reduces one quantity, lanes 0 / 16 broadcast.
+__device__ __forceinline__ void warp_sum2(double &a, double &b, int lane) {
+    const bool lo = lane < 16;
+    double mine = lo ? a : b;
+    const double give = lo ? b : a;
+    mine += shfl_xor(give, 16);
+#pragma unroll
+    for (int s = 8; s > 0; s >>= 1) mine += shfl_xor(mine, s);
+    a = shfl_idx(mine, 0);
+    b = shfl_idx(mine, 16);
+}
+
+// EXACT: N == 32 M, so the only lane with a missing right-hand element is lane 31 (local row M-1).
+template <int M, int WARPS, int MINB, bool EXACT>
 __global__ void __launch_bounds__(WARPS * 32, MINB) fom_picard_kernel(const FomParams p) {
     using L = FomSmem<M>;
     extern __shared__ __align__(16) double smem[];
-    double *s_off = smem;             // h/6 - At E / h         (off-diagonal constant of A)
-    double *s_hc = s_off + L::EL;     // At h / 8               (At * tau/2 numerator of SUPG)
-    double *s_rh = s_hc + L::EL;      // 1 / h
-    double *s_h6 = s_rh + L::EL;      // h / 6                  (mass off-diagonal)
-    double *s_a6 = s_h6 + L::EL;      // At / 6 (0 for elements that do not exist)
-    double *s_dg = s_a6 + L::EL;      // diagonal constant of A (1 for padded rows)
+    double *s_off = smem;             // h/6 - At E / h   (off-diagonal constant of A; 0 where no element)
+    double *s_h6 = s_off + L::EL;     // h/6              (mass off-diagonal; read once per time step)
+    double *s_dg = s_h6 + L::EL;      // diagonal constant of A (1 for padded rows)
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
-    double *w_fs = s_dg + L::NL + warp * L::PER_WARP;  // f_gp1 + f_gp2 per element
-    double *w_atf = w_fs + L::EL;                      // At * F per node
-    double *w_bn = w_atf + L::NL;                      // M U^n + At F per node (per time step)
+    double *w_hfs = s_dg + L::NL + warp * L::PER_WARP;  // (h/6) (f_gp1 + f_gp2) per element
+    double *w_atf = w_hfs + L::EL;                      // At * F per node
+    double *w_bn = w_atf + L::NL;                       // M U^n + At F per node (per time step)
 
     const int N = p.N;
     const double At = p.At;
@@ -68,16 +80,13 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) fom_picard_kernel(const FomP
     for (int idx = threadIdx.x; idx < L::EL; idx += WARPS * 32) {
         const int l = idx & 31, jj = (idx >> 5) - 1;
         const int e = l * M + jj;
-        double off = 0.0, hc = 0.0, rh = 0.0, h6 = 0.0, a6 = 0.0;
+        double off = 0.0, h6 = 0.0;
         if (e >= 0 && e <= N - 2) {
             const double h = p.X[e + 1] - p.X[e];
             h6 = h / 6.0;
-            rh = 1.0 / h;
-            off = h6 - At * p.E * rh;
-            hc = 0.125 * At * h;
-            a6 = At / 6.0;
+            off = h6 - At * p.E / h;
         }
-        s_off[idx] = off; s_hc[idx] = hc; s_rh[idx] = rh; s_h6[idx] = h6; s_a6[idx] = a6;
+        s_off[idx] = off; s_h6[idx] = h6;
     }
     for (int idx = threadIdx.x; idx < L::NL; idx += WARPS * 32) {
         const int l = idx & 31, j = idx >> 5;
@@ -94,6 +103,17 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) fom_picard_kernel(const FomP
 
     const int node0 = lane * M;
     const bool vec_ok = (node0 + M <= N) && ((N & 1) == 0) && ((M & 1) == 0);
+    // Elements that do not exist must contribute nothing.  Padded nodes carry u = 0, so every
+    // missing element has p = q = G = 0 by itself except the one to the right of the last real
+    // node (u1 != 0): its p, q, G are zeroed explicitly on local row jl of the lane that owns
+    // node N-1.  The element to the left of a lane (j = -1) is missing on lane 0 only (row 0 is
+    // the Dirichlet row there) and on fully padded lanes.
+    const int jl = N - 1 - node0;   // local index of the last real row (may be outside [0, M))
+    const double a6 = At / 6.0;     // convection: p = a6 (2 u1 + u2), q = a6 (u1 + 2 u2)
+    const double c1 = 1.5 * At;     // SUPG: At g = c1 (s du / 6 - (h/6) fsum) / max(|s|, 2e-10),  s = u1 + u2
+    const bool leftv = lane > 0 && jl >= 0;
+    const double a6L = leftv ? a6 : 0.0;
+    const double c1L = leftv ? c1 : 0.0;
 
     for (;;) {
         int s = 0;
@@ -110,19 +130,19 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) fom_picard_kernel(const FomP
 #pragma unroll
             for (int jj = -1; jj < M; ++jj) {
                 const int e = node0 + jj;
-                double fsum = 0.0, c0 = 0.0, c1 = 0.0;
+                double hfs = 0.0, c0 = 0.0, cr = 0.0;
                 if (e >= 0 && e <= N - 2) {
                     const double x1 = p.X[e], x2 = p.X[e + 1];
                     const double f1 = 0.02 * exp(mu2 * (BX_GA * x1 + BX_GB * x2));
                     const double f2 = 0.02 * exp(mu2 * (BX_GB * x1 + BX_GA * x2));
                     const double dV = 0.5 * (x2 - x1);
-                    fsum = f1 + f2;
+                    hfs = ((x2 - x1) / 6.0) * (f1 + f2);
                     c0 = (f1 * BX_GA + f2 * BX_GB) * dV;  // local node 1 of element e -> node e
-                    c1 = (f1 * BX_GB + f2 * BX_GA) * dV;  // local node 2 of element e -> node e+1
+                    cr = (f1 * BX_GB + f2 * BX_GA) * dV;  // local node 2 of element e -> node e+1
                 }
-                w_fs[(jj + 1) * 32 + lane] = fsum;
+                w_hfs[(jj + 1) * 32 + lane] = hfs;
                 if (jj >= 0) w_atf[jj * 32 + lane] = At * (left + c0);
-                left = c1;
+                left = cr;
             }
         }
 
@@ -161,16 +181,15 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) fom_picard_kernel(const FomP
                 // ================= one Picard iteration (:667-698) ======================
                 const double uL = shfl_up(u[M - 1], 1), uR = shfl_down(u[0], 1);
                 double cs[M], rs[M], fs[M];
+                Continuant<M> ct;
                 // element j = -1 (shared with the previous lane)
                 double offL, qL, GL;
                 {
                     const double u1 = uL, u2 = u[0];
                     const double sm = u1 + u2;
-                    const double t = s_a6[lane] * sm;
-                    qL = fma(s_a6[lane], u2, t);
-                    const double vel = fmax(fabs(0.5 * sm), 1.0e-10);
-                    const double z = fma(sm, (u2 - u1) * s_rh[lane], -w_fs[lane]);
-                    GL = (s_hc[lane] * rcp(vel)) * z;
+                    qL = fma(a6L, u2, a6L * sm);
+                    const double z = fma(sm * (u2 - u1), 1.0 / 6.0, -w_hfs[lane]);
+                    GL = (c1L * rcp(fmax(fabs(sm), 2.0e-10))) * z;
                     offL = s_off[lane];
                 }
 #pragma unroll
@@ -180,14 +199,13 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) fom_picard_kernel(const FomP
                     const double up = (j == M - 1) ? uR : u[j < M - 1 ? j + 1 : j];
                     const double u1 = u[j], u2 = up;
                     // element j: convection p, q (:418) and SUPG G = At*g (:569-575)
-                    const double a6 = s_a6[ei];
                     const double sm = u1 + u2;
                     const double t = a6 * sm;
-                    const double pe = fma(a6, u1, t);
-                    const double qe = fma(a6, u2, t);
-                    const double vel = fmax(fabs(0.5 * sm), 1.0e-10);
-                    const double z = fma(sm, (u2 - u1) * s_rh[ei], -w_fs[ei]);
-                    const double Ge = (s_hc[ei] * rcp(vel)) * z;
+                    double pe = fma(a6, u1, t);
+                    double qe = fma(a6, u2, t);
+                    const double z = fma(sm * (u2 - u1), 1.0 / 6.0, -w_hfs[ei]);
+                    double Ge = (c1 * rcp(fmax(fabs(sm), 2.0e-10))) * z;
+                    if ((!EXACT || j == M - 1) && j == jl) { pe = 0.0; qe = 0.0; Ge = 0.0; }
                     const double off = s_off[ei];
                     // row j of A, b and r = -R = b - A U_k
                     double a = offL - qL;
@@ -198,38 +216,13 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) fom_picard_kernel(const FomP
                     if (j == 0 && lane == 0) {  // Dirichlet row (:679-680, :686)
                         a = 0.0; b = 1.0; c = 0.0; r = mu1 - u1;
                     }
-                    // normalised Thomas sweep, carrying the coupling fs to the previous lane
-                    if (j == 0) {
-                        const double inv = rcp(b);
-                        cs[0] = c * inv; rs[0] = r * inv; fs[0] = a * inv;
-                    } else {
-                        const int jm = j > 0 ? j - 1 : 0;
-                        const double inv = rcp(fma(-a, cs[jm], b));
-                        cs[j] = c * inv;
-                        rs[j] = fma(-a, rs[jm], r) * inv;
-                        fs[j] = (-a * fs[jm]) * inv;
-                    }
+                    // local Thomas sweep in continuant form (no reciprocal in the dependent chain)
+                    ct.row(j, a, b, c, r, cs[j], rs[j], fs[j]);
                     offL = off; qL = qe; GL = Ge;
                 }
-                // upward sweep: row 0 of the lane as  F P + x_0 + G L = R  (L = own last unknown)
-                double F = fs[M - 2], G = cs[M - 2], R = rs[M - 2];
-#pragma unroll
-                for (int j = M - 3; j >= 0; --j) {
-                    F = fma(-cs[j], F, fs[j]);
-                    G = -cs[j] * G;
-                    R = fma(-cs[j], R, rs[j]);
-                }
-                // reduced row of this lane in the lanes' last unknowns
-                const double Fn = shfl_down(F, 1), Gn = shfl_down(G, 1), Rn = shfl_down(R, 1);
-                const double cl = (lane == 31) ? 0.0 : cs[M - 1];
-                const double be = fma(-cl, Fn, 1.0);
-                const double inv = rcp(be);
-                const double al = fs[M - 1] * inv;
-                const double ga = (-cl * Gn) * inv;
-                const double rho = fma(-cl, Rn, rs[M - 1]) * inv;
-                const double xl = warp_pcr_unit_diag(al, ga, rho, lane);
-                double P = shfl_up(xl, 1);
-                if (lane == 0) P = 0.0;
+                // condense each lane to one row, PCR across the lanes, hand P to the next lane
+                double xl, P;
+                partition_condense<M>(cs, rs, fs, lane, xl, P);
                 // back-substitution fused with the update and the two norms (:695-698)
                 double x = xl;
                 sd = 0.0; su = 0.0;
@@ -240,8 +233,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) fom_picard_kernel(const FomP
                     u[j] += x;
                     su = fma(u[j], u[j], su);
                 }
-                sd = warp_sum(sd);
-                su = warp_sum(su);
+                warp_sum2(sd, su, lane);
                 ++k;
             } while (sd > p.tol2 * su && k < p.kmax);
 
@@ -259,11 +251,11 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) fom_picard_kernel(const FomP
     }
 }
 
-template <int M, int WARPS, int MINB>
-static int launch_fom(const FomParams &p, cudaStream_t st) {
+template <int M, int WARPS, int MINB, bool EXACT>
+static int launch_fom_t(const FomParams &p, cudaStream_t st) {
     using L = FomSmem<M>;
     const size_t smem = L::bytes(WARPS);
-    auto kern = fom_picard_kernel<M, WARPS, MINB>;
+    auto kern = fom_picard_kernel<M, WARPS, MINB, EXACT>;
     BX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int dev = 0, sms = 0, occ = 0;
     BX_CUDA(cudaGetDevice(&dev));
@@ -279,6 +271,11 @@ static int launch_fom(const FomParams &p, cudaStream_t st) {
     return BX_OK;
 }
 
+template <int M, int WARPS, int MINB>
+static int launch_fom(const FomParams &p, cudaStream_t st) {
+    return (p.N == 32 * M) ? launch_fom_t<M, WARPS, MINB, true>(p, st) : launch_fom_t<M, WARPS, MINB, false>(p, st);
+}
+
 }  // namespace bx
 
 extern "C" long long bx_workspace_bytes(void) { return 256; }
@@ -291,8 +288,8 @@ extern "C" int bx_fom_picard_trajectories(int B, int N, int nsteps, const double
     BX_REQUIRE(B >= 0 && nsteps >= 0, "B and nsteps must be non-negative");
     BX_REQUIRE(N >= 2, "need at least 2 nodes (got N = %d)", N);
     BX_REQUIRE(kmax >= 1, "kmax must be >= 1 (the reference loop body defines U1)");
-    BX_REQUIRE(X && u0 && mu1 && mu2 && U && workspace, "null device pointer");
     if (B == 0) return BX_OK;
+    BX_REQUIRE(X && u0 && mu1 && mu2 && U && workspace, "null device pointer");
     FomParams p;
     p.B = B; p.N = N; p.nsteps = nsteps; p.kmax = kmax;
     p.X = X; p.u0 = u0; p.u0_stride = u0_batched ? N : 0;
@@ -302,7 +299,13 @@ extern "C" int bx_fom_picard_trajectories(int B, int N, int nsteps, const double
     if (N <= 64) return launch_fom<2, 4, 4>(p, st);
     if (N <= 128) return launch_fom<4, 4, 4>(p, st);
     if (N <= 256) return launch_fom<8, 4, 4>(p, st);
-    if (N <= 512) return launch_fom<16, 4, 3>(p, st);
+    if (N <= 512) {
+        // tuning knob (undocumented, for A/B runs on the box): BX_FOM_VARIANT=1 -> 16 warps/CTA at 128 regs
+        const char *v = getenv("BX_FOM_VARIANT");
+        if (v && v[0] == '1') return launch_fom<16, 16, 1>(p, st);
+        if (v && v[0] == '2') return launch_fom<16, 8, 1>(p, st);
+        return launch_fom<16, 4, 3>(p, st);
+    }
     if (N <= 1024) return launch_fom<32, 4, 1>(p, st);
     set_error("bx_fom_picard_trajectories: N = %d > 1024 needs the multi-CTA cyclic-reduction path", N);
     return BX_ERR_UNSUPPORTED;

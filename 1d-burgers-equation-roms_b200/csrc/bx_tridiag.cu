@@ -59,6 +59,7 @@ tridiag_solve_update_kernel(int B, int N, const double *__restrict__ dl, const d
 
     const int base = lane * (M + 1);
     double cs[M], rs[M], fs[M];
+    Continuant<M> ct;
 #pragma unroll
     for (int j = 0; j < M; ++j) {
         double a = t_a[base + j];
@@ -67,33 +68,13 @@ tridiag_solve_update_kernel(int B, int N, const double *__restrict__ dl, const d
         const double r = -t_r[base + j];
         if (lane == 0 && j == 0) a = 0.0;            // dl[0] is unused by contract
         if (lane * M + j >= N - 1) c = 0.0;          // du[N-1] is unused by contract
-        if (j == 0) {
-            const double inv = rcp(bb);
-            cs[0] = c * inv; rs[0] = r * inv; fs[0] = a * inv;
-        } else {
-            const int jm = j > 0 ? j - 1 : 0;
-            const double inv = rcp(fma(-a, cs[jm], bb));
-            cs[j] = c * inv;
-            rs[j] = fma(-a, rs[jm], r) * inv;
-            fs[j] = (-a * fs[jm]) * inv;
-        }
+        ct.row(j, a, bb, c, r, cs[j], rs[j], fs[j]);
     }
     __syncwarp();
     stage_in<M>(t_a, Uk + o, N, lane, 0.0, vec);  // reuse the dl tile for U_k
 
-    double F = fs[M - 2], G = cs[M - 2], Rr = rs[M - 2];
-#pragma unroll
-    for (int j = M - 3; j >= 0; --j) {
-        F = fma(-cs[j], F, fs[j]);
-        G = -cs[j] * G;
-        Rr = fma(-cs[j], Rr, rs[j]);
-    }
-    const double Fn = shfl_down(F, 1), Gn = shfl_down(G, 1), Rn = shfl_down(Rr, 1);
-    const double cl = (lane == 31) ? 0.0 : cs[M - 1];
-    const double inv = rcp(fma(-cl, Fn, 1.0));
-    const double xl = warp_pcr_unit_diag(fs[M - 1] * inv, (-cl * Gn) * inv, fma(-cl, Rn, rs[M - 1]) * inv, lane);
-    double P = shfl_up(xl, 1);
-    if (lane == 0) P = 0.0;
+    double xl, P;
+    partition_condense<M>(cs, rs, fs, lane, xl, P);
     __syncwarp();
     double x = xl, sd = 0.0, su = 0.0;
 #pragma unroll

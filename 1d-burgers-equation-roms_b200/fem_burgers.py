@@ -203,6 +203,8 @@ class FEMBurgers:
             raise ValueError("out must be a contiguous float64 tensor of shape (B, nTimeSteps+1, N)")
         iters = iters_out if iters_out is not None else self._new(B, nT, dtype=torch.int32)
         lib = _lib.load()
+        if B == 0:
+            return U, iters
         _lib.check(lib.bx_fom_picard_trajectories(B, N, nT, _ptr(self.Xd), _ptr(u0), batched, _ptr(mu1),
                                                   _ptr(mu2), float(At), float(E), float(tol), int(kmax),
                                                   _ptr(U), _ptr(iters), _ptr(self._workspace()), _stream()),

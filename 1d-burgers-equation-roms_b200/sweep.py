@@ -1,0 +1,114 @@
+"""Host-side sweep drivers: the batched replacement of the reference's
+`for (mu1, mu2) in all_samples:` loop (FEM/paper_training_stage.py:8-10, 28-53).
+
+  * parameter_grid      — the reference's mu1-major Cartesian grid (:8-10)
+  * shard_range         — contiguous block of samples per rank (one process per GPU; samples are
+                          independent, so the data path needs no collective)
+  * fom_sweep_to_host   — streams a sweep whose parameters and results live in HOST memory:
+                          H2D of the parameters, fused trajectory kernel, D2H of the snapshots
+                          into pinned buffers, chunk by chunk, copy overlapped with compute
+  * snapshot_filename   — the reference's on-disk name (:52)
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+
+def parameter_grid(n1=64, n2=64, mu1_range=(4.25, 5.5), mu2_range=(0.015, 0.03)):
+    """[[mu1, mu2] for mu1 in linspace(...) for mu2 in linspace(...)] — mu1-major."""
+    mu1 = np.linspace(mu1_range[0], mu1_range[1], n1)
+    mu2 = np.linspace(mu2_range[0], mu2_range[1], n2)
+    return np.repeat(mu1, n2), np.tile(mu2, n1)
+
+
+def shard_range(n_samples: int, rank: int, world: int):
+    """Contiguous block [lo, hi) of rank `rank`; remainders go to the first ranks."""
+    base, rem = divmod(int(n_samples), int(world))
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def snapshot_filename(mu1: float, mu2: float) -> str:
+    return f"fem_simulation_mu1_{mu1:.3f}_mu2_{mu2:.4f}.npy"
+
+
+class HostSweepBuffers:
+    """Pinned host staging + device buffers for fom_sweep_to_host (allocate once, reuse)."""
+
+    def __init__(self, fem, chunk: int, nTimeSteps: int):
+        N = fem.n_nodes
+        self.chunk, self.nT, self.N = int(chunk), int(nTimeSteps), N
+        dev = fem.device
+        self.dU = [torch.empty((chunk, nTimeSteps + 1, N), dtype=torch.float64, device=dev) for _ in range(2)]
+        self.dIt = [torch.empty((chunk, nTimeSteps), dtype=torch.int32, device=dev) for _ in range(2)]
+        self.dMu = [torch.empty((2, chunk), dtype=torch.float64, device=dev) for _ in range(2)]
+        self.hU = [torch.empty((chunk, nTimeSteps + 1, N), dtype=torch.float64).pin_memory() for _ in range(2)]
+        self.hIt = [torch.empty((chunk, nTimeSteps), dtype=torch.int32).pin_memory() for _ in range(2)]
+        self.copy_stream = torch.cuda.Stream(device=dev)
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+
+
+def fom_sweep_to_host(fem, At, nTimeSteps, u0, mu1, mu2, E=0.0, chunk=1024, consumer=None,
+                      buffers: HostSweepBuffers | None = None, tol=1e-6, kmax=20):
+    """FOM sweep with HOST inputs and HOST outputs.
+
+    mu1, mu2: pinned (or pageable) host float64 tensors / numpy arrays of shape (B,).
+    consumer(lo, hi, U_host, iters_host) is called for each finished chunk with pinned-memory
+    views U_host (hi-lo, nTimeSteps+1, N), iters_host (hi-lo, nTimeSteps); the views are reused two
+    chunks later, so the consumer must copy or write out what it keeps (the reference writes
+    one .npy per sample, FEM/paper_training_stage.py:52-53).
+    Returns the total number of nonlinear iterations (int).
+    """
+    mu1 = torch.as_tensor(mu1, dtype=torch.float64)
+    mu2 = torch.as_tensor(mu2, dtype=torch.float64)
+    B = mu1.numel()
+    buf = buffers or HostSweepBuffers(fem, min(chunk, max(B, 1)), nTimeSteps)
+    chunk = buf.chunk
+    u0d = fem._dev(u0)
+    if u0d.numel() != fem.n_nodes:
+        raise ValueError("fom_sweep_to_host takes one shared initial condition u0 (N,)")
+    compute = torch.cuda.current_stream()
+    done = [None, None]      # kernel finished on buffer i
+    copied = [None, None]    # D2H finished on buffer i
+    pending = [None, None]   # (lo, hi) waiting for the consumer
+    total_iters = 0
+    buf.h2d_bytes = 0
+    buf.d2h_bytes = 0
+
+    def drain(i):
+        nonlocal total_iters
+        if pending[i] is None:
+            return
+        copied[i].synchronize()
+        lo, hi = pending[i]
+        total_iters += int(buf.hIt[i][: hi - lo].sum())
+        if consumer is not None:
+            consumer(lo, hi, buf.hU[i][: hi - lo], buf.hIt[i][: hi - lo])
+        pending[i] = None
+
+    for c, lo in enumerate(range(0, B, chunk)):
+        hi = min(B, lo + chunk)
+        n = hi - lo
+        i = c & 1
+        drain(i)  # host + device buffer i are free again
+        buf.dMu[i][0, :n].copy_(mu1[lo:hi], non_blocking=True)
+        buf.dMu[i][1, :n].copy_(mu2[lo:hi], non_blocking=True)
+        buf.h2d_bytes += 2 * n * 8
+        fem.fom_burgers_batch(At, nTimeSteps, u0d, buf.dMu[i][0, :n], E, buf.dMu[i][1, :n],
+                              out=buf.dU[i][:n], iters_out=buf.dIt[i][:n], tol=tol, kmax=kmax)
+        done[i] = torch.cuda.Event()
+        done[i].record(compute)
+        with torch.cuda.stream(buf.copy_stream):
+            buf.copy_stream.wait_event(done[i])
+            buf.hU[i][:n].copy_(buf.dU[i][:n], non_blocking=True)
+            buf.hIt[i][:n].copy_(buf.dIt[i][:n], non_blocking=True)
+            copied[i] = torch.cuda.Event()
+            copied[i].record(buf.copy_stream)
+        # device buffer i is next written by chunk c+2, after drain(i) has waited for this copy
+        buf.d2h_bytes += n * ((nTimeSteps + 1) * fem.n_nodes * 8 + nTimeSteps * 4)
+        pending[i] = (lo, hi)
+    drain(0)
+    drain(1)
+    return total_iters
