@@ -29,6 +29,10 @@ SIGNATURES = {
     "bx_workspace_bytes": (c_longlong, []),
     "bx_fom_picard_trajectories": (c_int, [c_int, c_int, c_int, P, P, c_int, P, P, c_double, c_double,
                                            c_double, c_int, P, P, P, P]),
+    "bx_fom_newton_trajectories": (c_int, [c_int, c_int, c_int, P, P, c_int, P, P, c_double, c_double,
+                                           c_double, c_double, c_int, P, P, P, P]),
+    "bx_prom_trajectories": (c_int, [c_int, c_int, c_int, c_int, P, P, c_int, P, P, c_double, c_double,
+                                     P, c_int, c_double, c_int, P, P, P, P]),
 }
 
 _lib = None

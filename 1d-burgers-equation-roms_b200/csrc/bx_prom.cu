@@ -38,6 +38,7 @@ struct PromParams {
     const double *mu2;
     double At, E, tol;
     const double *Phi;  // (N, n) row-major (C order), shared by all samples
+    int phi_smem;       // 1: the CTA keeps a permuted copy of Phi in shared memory; 0: read from global / L2
     double *U;
     int *iters;
     unsigned int *counter;
@@ -74,21 +75,26 @@ struct PromGeom {
 struct PromSmem {
     int phi, h6, ke, per_cta;  // CTA-wide: permuted Phi (NP x n), h/6 and At E / h per element
     int u, rows, bn, hfs, atf, q, misc, per_group;
-    __host__ __device__ static PromSmem make(int NP, int S, int n, int NC) {
+    __host__ __device__ static PromSmem make(int NP, int S, int n, int NC, int tiles, int phi_smem) {
         PromSmem m;
         int o = 0;
-        m.phi = o; o += NP * n; o = (o + 1) & ~1;
+        m.phi = o; o += phi_smem ? NP * n : 0; o = (o + 1) & ~1;
         m.h6 = o; o += NP + 2;   // element e at index e + 1 (e = -1 .. NP-1)
         m.ke = o; o += NP + 2;
         m.per_cta = (o + 1) & ~1;
         o = 0;
-        m.rows = o; o += 4 * NP;         // (dl, d, du, R) per permuted row; reused as reduction scratch
+        // (dl, d, du, R) per permuted row; reused as scratch for the cross-warp reduction
+        // ([2][tiles][32][2]) and then for the dense reduced system (NC x (NC+1))
+        int rows = 4 * NP;
+        if (rows < 2 * tiles * 64) rows = 2 * tiles * 64;
+        if (rows < NC * (NC + 1)) rows = NC * (NC + 1);
+        m.rows = o; o += (rows + 1) & ~1;
         m.u = o; o += NP + NP / S + 4;   // U_k, skewed natural order, one halo entry on each side
         o = (o + 1) & ~1;
         m.bn = o; o += NP;               // M U^n + At F
         m.hfs = o; o += NP + 2;          // (h/6)(f_gp1 + f_gp2) per element, index e + 1
         m.atf = o; o += NP;              // At F
-        m.q = o; o += 2 * NC;            // q (NC) and warp-partial q0 staging
+        m.q = o; o += 2 * NC + 4 * NC;   // q (padded to 2 NC) and the four warps' q0 partials
         m.misc = o; o += 4;              // sample id / loop flags (as ints)
         m.per_group = (o + 1) & ~1;
         return m;
@@ -169,7 +175,7 @@ __global__ void __launch_bounds__(G * PGT, 1) prom_kernel(const PromParams p) {
     const int N = p.N, n = p.n;
     const PromGeom geo = PromGeom::make(N);
     const int S = geo.S, lgS = geo.lgS, NP = geo.NP;
-    const PromSmem lay = PromSmem::make(NP, S, n, NC);
+    const PromSmem lay = PromSmem::make(NP, S, n, NC, TILES, p.phi_smem);
     double *s_phi = smem + lay.phi;
     double *s_h6 = smem + lay.h6;
     double *s_ke = smem + lay.ke;
@@ -190,9 +196,11 @@ __global__ void __launch_bounds__(G * PGT, 1) prom_kernel(const PromParams p) {
     const double At = p.At;
 
     // ---- CTA prologue: permuted Phi and mesh constants ------------------------------------
-    for (int idx = threadIdx.x; idx < NP * n; idx += G * PGT) {
-        const int i = idx / n, j = idx - i * n;
-        s_phi[perm_row(i, S, lgS) * n + j] = (i < N) ? p.Phi[idx] : 0.0;
+    if (p.phi_smem) {
+        for (int idx = threadIdx.x; idx < NP * n; idx += G * PGT) {
+            const int i = idx / n, j = idx - i * n;
+            s_phi[perm_row(i, S, lgS) * n + j] = (i < N) ? p.Phi[idx] : 0.0;
+        }
     }
     for (int idx = threadIdx.x; idx < NP + 2; idx += G * PGT) {
         const int e = idx - 1;
@@ -210,8 +218,13 @@ __global__ void __launch_bounds__(G * PGT, 1) prom_kernel(const PromParams p) {
     const double c1 = 1.5 * At;
     // phase-B/D constants of this thread: first node of its run, its Phi rows, its columns
     const int run0 = ((w << 2) + t) << lgS;                 // natural index of the run's first node
-    const double *phi_run = s_phi + (size_t)(((w << lgS) << 2) + t) * n;   // permuted row of (w, s = 0, t)
-    const int row_stride = 4 * n;                           // s -> s + 1
+    // Phi row of natural node i: permuted shared-memory copy, or the caller's array (rows >= N are
+    // never dereferenced there: see rowok below)
+    const bool phis = p.phi_smem != 0;
+    const double *phi_run = phis ? s_phi + (size_t)(((w << lgS) << 2) + t) * n   // permuted row of (w, s = 0, t)
+                                 : p.Phi + (size_t)run0 * n;
+    const int row_stride = phis ? 4 * n : n;                // s -> s + 1
+    const int nreal = phis ? NP : N;                        // rows that may be dereferenced
     const int jR = n >> 3, gR = n & 7;                      // block / lane-group of the R column
     bool colok[NB];
 #pragma unroll
@@ -322,11 +335,12 @@ __global__ void __launch_bounds__(G * PGT, 1) prom_kernel(const PromParams p) {
                 {
                     double pm[NB], p0[NB], pp[NB];
                     {
-                        const double *rm = s_phi + (size_t)perm_row(run0 > 0 ? run0 - 1 : 0, S, lgS) * n;
+                        const int im = run0 > 0 ? run0 - 1 : 0;
+                        const double *rm = phis ? s_phi + (size_t)perm_row(im, S, lgS) * n : p.Phi + (size_t)im * n;
 #pragma unroll
                         for (int b = 0; b < NB; ++b) {
-                            pm[b] = (colok[b] && run0 > 0) ? rm[b * 8 + g] : 0.0;
-                            p0[b] = colok[b] ? phi_run[b * 8 + g] : 0.0;
+                            pm[b] = (colok[b] && run0 > 0 && im < nreal) ? rm[b * 8 + g] : 0.0;
+                            p0[b] = (colok[b] && run0 < nreal) ? phi_run[b * 8 + g] : 0.0;
                         }
                     }
                     const double2 *rows = reinterpret_cast<const double2 *>(g_rows) + 2 * ((((w << lgS)) << 2) + t);
@@ -334,11 +348,13 @@ __global__ void __launch_bounds__(G * PGT, 1) prom_kernel(const PromParams p) {
 #pragma unroll 2
                     for (int s = 0; s < S; ++s) {
                         // Phi row of node run0 + s + 1 (next run's first row at the end of this one)
+                        const int inx = run0 + s + 1;
                         const double *rp = (s + 1 < S) ? phi_run + (size_t)(s + 1) * row_stride
-                                                       : s_phi + (size_t)perm_row(run0 + S < NP ? run0 + S : 0, S, lgS) * n;
-                        const bool lastrow = (s + 1 == S) && (run0 + S >= NP);
+                                           : phis  ? s_phi + (size_t)perm_row(inx < NP ? inx : 0, S, lgS) * n
+                                                   : p.Phi + (size_t)(inx < N ? inx : 0) * n;
+                        const bool rowok = inx < nreal;
 #pragma unroll
-                        for (int b = 0; b < NB; ++b) pp[b] = (colok[b] && !lastrow) ? rp[b * 8 + g] : 0.0;
+                        for (int b = 0; b < NB; ++b) pp[b] = (colok[b] && rowok) ? rp[b * 8 + g] : 0.0;
                         const double2 ab = rows[8 * s], cr = rows[8 * s + 1];
                         const double uk = up[s];
                         double jp[NB];
@@ -372,7 +388,7 @@ __global__ void __launch_bounds__(G * PGT, 1) prom_kernel(const PromParams p) {
 
                 // ---- cross-warp reduction, fixed order (w0 + w2) + (w1 + w3) ----------------
                 double *scr = g_rows;                       // [2][TILES][32][2]
-                double *scq = g_rows + 2 * TILES * 64;      // [4][NC] q0 partials
+                double *scq = g_q + 2 * NC;                 // [4][NC] q0 partials
                 if (t == 0) {
 #pragma unroll
                     for (int b = 0; b < NB; ++b) scq[w * NC + b * 8 + g] = pq[b];
@@ -403,7 +419,7 @@ __global__ void __launch_bounds__(G * PGT, 1) prom_kernel(const PromParams p) {
                     for (int i = 0; i < TILES; ++i) { const double2 v = d2[i * 32]; acc[i][0] += v.x; acc[i][1] += v.y; }
                     __syncwarp();
                     // spread the accumulator tiles into a dense (NC x (NC+1)) matrix; column n = br
-                    double *mat = g_rows + 2 * TILES * 64 + 4 * NC;   // behind the q0 partials
+                    double *mat = g_rows;   // over the reduction scratch (this warp has consumed it)
                     constexpr int LD = NC + 1;
 #pragma unroll
                     for (int I = 0; I < NB; ++I) {
@@ -447,7 +463,7 @@ __global__ void __launch_bounds__(G * PGT, 1) prom_kernel(const PromParams p) {
                         const double *r0 = phi_run + (size_t)s * row_stride;
                         double v = 0.0;
 #pragma unroll
-                        for (int b = 0; b < NB; ++b) v = fma(colok[b] ? r0[b * 8 + g] : 0.0, qv[b], v);
+                        for (int b = 0; b < NB; ++b) v = fma((colok[b] && run0 + s < nreal) ? r0[b * 8 + g] : 0.0, qv[b], v);
                         v += shfl_xor(v, 4);
                         v += shfl_xor(v, 8);
                         v += shfl_xor(v, 16);
@@ -469,9 +485,10 @@ __global__ void __launch_bounds__(G * PGT, 1) prom_kernel(const PromParams p) {
 }
 
 template <int NB, int G, bool LSPG>
-static int launch_prom_t(const PromParams &p, cudaStream_t st, bool *fits) {
+static int launch_prom_t(PromParams p, int phi_smem, cudaStream_t st, bool *fits) {
     const PromGeom geo = PromGeom::make(p.N);
-    const PromSmem lay = PromSmem::make(geo.NP, geo.S, p.n, NB * 8);
+    p.phi_smem = phi_smem;
+    const PromSmem lay = PromSmem::make(geo.NP, geo.S, p.n, NB * 8, PromTiles<NB, LSPG>::COUNT, phi_smem);
     const size_t smem = sizeof(double) * ((size_t)lay.per_cta + (size_t)G * lay.per_group);
     int dev = 0, sms = 0, maxsm = 0;
     BX_CUDA(cudaGetDevice(&dev));
@@ -493,12 +510,16 @@ static int launch_prom_t(const PromParams &p, cudaStream_t st, bool *fits) {
 template <int NB, bool LSPG>
 static int launch_prom_nb(const PromParams &p, cudaStream_t st) {
     bool fits = false;
-    int rc = launch_prom_t<NB, 3, LSPG>(p, st, &fits);
-    if (rc != BX_OK || fits) return rc;
-    rc = launch_prom_t<NB, 2, LSPG>(p, st, &fits);
-    if (rc != BX_OK || fits) return rc;
-    rc = launch_prom_t<NB, 1, LSPG>(p, st, &fits);
-    if (rc != BX_OK || fits) return rc;
+    int rc;
+    // Phi in shared memory with as many trajectory groups per CTA as fit; else Phi from global / L2
+    for (int phi_smem = 1; phi_smem >= 0; --phi_smem) {
+        rc = launch_prom_t<NB, 3, LSPG>(p, phi_smem, st, &fits);
+        if (rc != BX_OK || fits) return rc;
+        rc = launch_prom_t<NB, 2, LSPG>(p, phi_smem, st, &fits);
+        if (rc != BX_OK || fits) return rc;
+        rc = launch_prom_t<NB, 1, LSPG>(p, phi_smem, st, &fits);
+        if (rc != BX_OK || fits) return rc;
+    }
     set_error("bx_prom_trajectories: N = %d, n = %d does not fit in shared memory", p.N, p.n);
     return BX_ERR_UNSUPPORTED;
 }

@@ -211,6 +211,69 @@ class FEMBurgers:
                    "bx_fom_picard_trajectories")
         return U, iters
 
+    def _sweep_args(self, u0, mu1, mu2, nTimeSteps, out, iters_out):
+        """Common argument handling of the trajectory entry points."""
+        mu1 = self._dev(mu1).reshape(-1)
+        mu2 = self._dev(mu2).reshape(-1)
+        B, N = mu1.numel(), self.n_nodes
+        if mu2.numel() != B:
+            raise ValueError("mu1 and mu2 must have the same number of samples")
+        u0 = self._dev(u0)
+        if u0.numel() == N:
+            batched = 0
+        elif u0.numel() == B * N:
+            batched = 1
+        else:
+            raise ValueError("u0 must have shape (N,) or (B, N)")
+        nT = int(nTimeSteps)
+        U = out if out is not None else self._new(B, nT + 1, N)
+        if tuple(U.shape) != (B, nT + 1, N) or U.dtype != torch.float64 or not U.is_contiguous():
+            raise ValueError("out must be a contiguous float64 tensor of shape (B, nTimeSteps+1, N)")
+        iters = iters_out if iters_out is not None else self._new(B, nT, dtype=torch.int32)
+        return mu1, mu2, u0, batched, B, N, nT, U, iters
+
+    @staticmethod
+    def _projection_code(projection):
+        """'Galerkin' / 'LSPG' exactly as the reference spells them (FEM/fem_burgers.py:754-764)."""
+        if projection == "Galerkin":
+            return _lib.BX_GALERKIN
+        if projection == "LSPG":
+            return _lib.BX_LSPG
+        raise ValueError(f"Projection method '{projection}' is not available. Please use 'Galerkin' or 'LSPG'.")
+
+    def fom_burgers_newton_batch(self, At, nTimeSteps, u0, mu1, E, mu2, out=None, iters_out=None,
+                                 lambda_=0.1, tol=1e-6, kmax=100):
+        """fom_burgers_newton as coded (FEM/fem_burgers.py:584) for B samples.
+        Returns U (B, nTimeSteps+1, N) and iters (B, nTimeSteps) int32, CUDA tensors."""
+        mu1, mu2, u0, batched, B, N, nT, U, iters = self._sweep_args(u0, mu1, mu2, nTimeSteps, out, iters_out)
+        if B == 0:
+            return U, iters
+        lib = _lib.load()
+        _lib.check(lib.bx_fom_newton_trajectories(B, N, nT, _ptr(self.Xd), _ptr(u0), batched, _ptr(mu1),
+                                                  _ptr(mu2), float(At), float(E), float(lambda_), float(tol),
+                                                  int(kmax), _ptr(U), _ptr(iters), _ptr(self._workspace()),
+                                                  _stream()), "bx_fom_newton_trajectories")
+        return U, iters
+
+    def pod_prom_burgers_batch(self, At, nTimeSteps, u0, mu1, E, mu2, Phi, projection="Galerkin", out=None,
+                               iters_out=None, tol=1e-6, kmax=20):
+        """pod_prom_burgers (FEM/fem_burgers.py:709) for B samples: mu1, mu2 (B,), Phi (N, n) shared.
+        Returns U (B, nTimeSteps+1, N) and iters (B, nTimeSteps) int32, CUDA tensors."""
+        code = self._projection_code(projection)
+        mu1, mu2, u0, batched, B, N, nT, U, iters = self._sweep_args(u0, mu1, mu2, nTimeSteps, out, iters_out)
+        Phi = self._dev(Phi)
+        if Phi.dim() != 2 or Phi.shape[0] != N:
+            raise ValueError("Phi must have shape (N, n)")
+        n = int(Phi.shape[1])
+        if B == 0:
+            return U, iters
+        lib = _lib.load()
+        _lib.check(lib.bx_prom_trajectories(B, N, n, nT, _ptr(self.Xd), _ptr(u0), batched, _ptr(mu1), _ptr(mu2),
+                                            float(At), float(E), _ptr(Phi), code, float(tol), int(kmax),
+                                            _ptr(U), _ptr(iters), _ptr(self._workspace()), _stream()),
+                   "bx_prom_trajectories")
+        return U, iters
+
     # ------------------------------------------------------------------ legacy surface (numpy / scipy in-out)
     def _csc(self, bands):
         import scipy.sparse as sp  # return type of the reference (:353); not used for any arithmetic here
@@ -242,3 +305,20 @@ class FEMBurgers:
                                        [float(mu2)])
         self.last_iters = it[0].cpu().numpy()
         return np.ascontiguousarray(U[0].cpu().numpy().T)
+
+    def fom_burgers_newton(self, At, nTimeSteps, u0, mu1, E, mu2):
+        """Drop-in for FEMBurgers.fom_burgers_newton (:584-643): returns ndarray (N, nTimeSteps+1)."""
+        U, it = self.fom_burgers_newton_batch(At, nTimeSteps, np.asarray(u0, dtype=np.float64), [float(mu1)], E,
+                                              [float(mu2)])
+        self.last_iters = it[0].cpu().numpy()
+        return np.ascontiguousarray(U[0].cpu().numpy().T)
+
+    def pod_prom_burgers(self, At, nTimeSteps, u0, mu1, E, mu2, Phi, projection="Galerkin"):
+        """Drop-in for FEMBurgers.pod_prom_burgers (:709-785): returns ndarray (N, nTimeSteps+1)."""
+        U, it = self.pod_prom_burgers_batch(At, nTimeSteps, np.asarray(u0, dtype=np.float64), [float(mu1)], E,
+                                            [float(mu2)], np.asarray(Phi, dtype=np.float64), projection)
+        self.last_iters = it[0].cpu().numpy()
+        return np.ascontiguousarray(U[0].cpu().numpy().T)
+
+    # the north_star's name for the same method
+    pod_prom_newton = pod_prom_burgers

@@ -89,6 +89,28 @@ int bx_fom_picard_trajectories(int B, int N, int nsteps, const double *X, const 
                                double At, double E, double tol, int kmax,
                                double *U, int *iters, void *workspace, void *stream);
 
+/* FEMBurgers.pod_prom_burgers, FEM/fem_burgers.py:709-785 (north_star alias pod_prom_newton), for B
+ * samples at once.  Phi: (N, n) row-major (C order) reduced basis shared by all samples.
+ * projection: BX_GALERKIN (Ar = Phi^T A Phi, br = Phi^T R, :756-757) or BX_LSPG (J = A Phi,
+ * Ar = J^T J, br = J^T R, :760-762); anything else returns BX_ERR_PROJECTION (ValueError, :764).
+ * The reduced solve is LU with partial pivoting (np.linalg.solve -> LAPACK gesv, :767).
+ * tol, kmax: the literals 1e-6 / 20 of :725.  1 <= n <= 31 in this build.                   */
+int bx_prom_trajectories(int B, int N, int n, int nsteps, const double *X, const double *u0,
+                         int u0_batched, const double *mu1, const double *mu2, double At, double E,
+                         const double *Phi, int projection, double tol, int kmax,
+                         double *U, int *iters, void *workspace, void *stream);
+
+/* FEMBurgers.fom_burgers_newton AS CODED, FEM/fem_burgers.py:584-643, for B samples at once.
+ * At :616 `At * dC_dU @ U0` is a matrix-vector product whose result numpy broadcasts onto every row:
+ * J = T + 1 w^T, T = M + At E K + At C(U_k), w = At dC_dU U_k, row 0 <- e0^T (:619-620).  Solved exactly
+ * with one tridiagonal factorisation and two right-hand sides (Sherman-Morrison).  R has no SUPG term
+ * (:623-626).  U_{k+1} = U_k + lambda delta; lambda, tol, kmax: the literals 0.1 / 1e-6 / 100 of
+ * :597-598, :606.  N <= 1024.                                                                */
+int bx_fom_newton_trajectories(int B, int N, int nsteps, const double *X, const double *u0,
+                               int u0_batched, const double *mu1, const double *mu2,
+                               double At, double E, double lambda, double tol, int kmax,
+                               double *U, int *iters, void *workspace, void *stream);
+
 #ifdef __cplusplus
 }
 #endif
