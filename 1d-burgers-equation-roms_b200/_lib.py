@@ -33,6 +33,8 @@ SIGNATURES = {
                                            c_double, c_double, c_int, P, P, P, P]),
     "bx_prom_trajectories": (c_int, [c_int, c_int, c_int, c_int, P, P, c_int, P, P, c_double, c_double,
                                      P, c_int, c_double, c_int, P, P, P, P]),
+    "bx_gram_workspace_bytes": (c_longlong, [c_int, c_longlong]),
+    "bx_gram_accumulate": (c_int, [c_int, c_longlong, P, P, c_int, P, P]),
 }
 
 _lib = None

@@ -111,6 +111,17 @@ int bx_fom_newton_trajectories(int B, int N, int nsteps, const double *X, const 
                                double At, double E, double lambda, double tol, int kmax,
                                double *U, int *iters, void *workspace, void *stream);
 
+/* ---- POD basis: snapshot Gram matrix (replaces np.linalg.svd of POD/pod.py:80-84) ------------ */
+/* G (+)= S S^T with S given as `cols` snapshots of N nodes, one snapshot per row -- i.e. the trajectory
+ * buffer U (B, nsteps+1, N) itself with cols = B*(nsteps+1).  G: (N, N) row-major, both triangles
+ * written.  accumulate != 0 adds to the G already there (several trajectory buffers, one G per GPU);
+ * the sum over GPUs is the caller's all-reduce (ncclAllReduce on N*N doubles).  FP64 tensor pipe (DMMA),
+ * fixed summation order (bit-reproducible for a given N, cols and SM count).
+ * workspace: bx_gram_workspace_bytes(N, cols) bytes, contents ignored.                                */
+long long bx_gram_workspace_bytes(int N, long long cols);
+int bx_gram_accumulate(int N, long long cols, const double *S, double *G, int accumulate,
+                       void *workspace, void *stream);
+
 #ifdef __cplusplus
 }
 #endif
