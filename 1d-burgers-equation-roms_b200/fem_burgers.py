@@ -84,6 +84,12 @@ class FEMBurgers:
             self._ws = torch.zeros(int(_lib.load().bx_workspace_bytes()), dtype=torch.uint8, device=self.device)
         return self._ws
 
+    def _scratch(self, nbytes):
+        """Grow-only device scratch for the entry points whose workspace depends on the batch size."""
+        if getattr(self, "_big_ws", None) is None or self._big_ws.numel() < nbytes:
+            self._big_ws = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
+        return self._big_ws
+
     def _dev(self, a, shape=None):
         """numpy / scalar / tensor -> contiguous float64 CUDA tensor."""
         if isinstance(a, torch.Tensor):
@@ -270,7 +276,8 @@ class FEMBurgers:
         lib = _lib.load()
         _lib.check(lib.bx_prom_trajectories(B, N, n, nT, _ptr(self.Xd), _ptr(u0), batched, _ptr(mu1), _ptr(mu2),
                                             float(At), float(E), _ptr(Phi), code, float(tol), int(kmax),
-                                            _ptr(U), _ptr(iters), _ptr(self._workspace()), _stream()),
+                                            _ptr(U), _ptr(iters),
+                                            _ptr(self._scratch(int(lib.bx_prom_workspace_bytes(B, N)))), _stream()),
                    "bx_prom_trajectories")
         return U, iters
 
