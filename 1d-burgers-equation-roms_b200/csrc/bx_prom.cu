@@ -73,19 +73,19 @@ struct PromGeom {
 // that the four k-lanes of an MMA step (nodes S apart) hit different banks.
 struct PromSmem {
     int phi, h6, per_cta;                 // CTA-wide: permuted Phi (NP x ldp), h/6 per element
-    int u, stage, bn, hfs, per_warp, arr;
+    int u, misc, bn, hfs, per_warp, arr;
     __host__ __device__ static PromSmem make(int NP, int ldp, int phi_smem) {
         PromSmem m;
         m.arr = NP + 8;
         int o = 0;
-        m.phi = o; o += phi_smem ? NP * ldp : 0; o = (o + 1) & ~1;
+        m.phi = o; o += phi_smem ? (NP + 4) * ldp : 0;   // + 4 wrap rows o = (o + 1) & ~1;
         m.h6 = o; o += m.arr;
         m.per_cta = (o + 1) & ~1;
         o = 0;
-        int usz = m.arr < 16 * MAT_LD - 8 ? 16 * MAT_LD - 8 : m.arr;   // u + first 8 of stage hold the 16 x 33 matrix
+        int usz = m.arr < 16 * MAT_LD - 8 ? 16 * MAT_LD - 8 : m.arr;   // u + first 8 of misc hold the 16 x 33 matrix
         usz = (usz + 1) & ~1;
         m.u = o; o += usz;
-        m.stage = o; o += 128;            // row staging; later q0 / pivot rows / q
+        m.misc = o; o += 128;             // q0 / pivot rows / q (and the tail of the matrix)
         m.bn = o; o += m.arr;             // M U^n + At F
         m.hfs = o; o += m.arr;            // (h/6)(f_gp1 + f_gp2) per element
         m.per_warp = (o + 1) & ~1;
@@ -123,12 +123,17 @@ __global__ void __launch_bounds__(256) prom_forcing_kernel(int B, int N, const d
     hfs[idx] = h;
 }
 
-// n x n solve with partial pivoting, one matrix row per lane (lane < n), columns in registers.
-// a[j] (j < n): row `lane` of Ar; rhs: -br[lane].  Returns x[lane] (solution component `lane`).
-// Same elimination order as LAPACK dgetf2 (first maximal |a_ik| among the remaining rows, scaling
-// by the reciprocal pivot); rows never move (implicit pivoting by lane).  The pivot row of step k
-// is published through a double-buffered shared-memory row (pb: 2 x (NC+2) doubles, 16-B aligned).
-template <int NC>
+// n x n solve, one matrix row per lane (lane < n), columns in registers.
+// a[j]: row `lane` of Ar (columns >= n and rows >= n may hold anything finite: they never act as
+// pivots and only receive harmless updates); rhs: -br[lane].  Returns x[lane].
+// PIVOT: partial pivoting in the elimination order of LAPACK dgetf2 (first maximal |a_ik| among the
+// remaining rows, scaling by the reciprocal pivot), as np.linalg.solve -> gesv does (:767); rows
+// never move (implicit pivoting by lane).  !PIVOT: the LSPG normal matrix J^T J is symmetric
+// positive definite, for which elimination in natural order is backward stable (it is the
+// Cholesky recurrence without the square roots).
+// The pivot row of step k is published through a double-buffered shared-memory row
+// (pb: 2 x (NC+2) doubles, 16-byte aligned), moved with 128-bit accesses.
+template <int NC, bool PIVOT>
 __device__ __forceinline__ double lu_solve_rows(double (&a)[NC], double rhs, int n, int lane, double *pb) {
     constexpr int PLD = NC + 2;
     bool avail = lane < n;   // row not yet used as a pivot row
@@ -137,31 +142,38 @@ __device__ __forceinline__ double lu_solve_rows(double (&a)[NC], double rhs, int
     double pinv = 0.0;       // 1 / pivot of the step this lane's row served
 #pragma unroll
     for (int k = 0; k < NC; ++k) {
-        pls[k] = 0;
+        pls[k] = k;
         if (k < n) {
-            // argmax |a[k]| over the available rows (idamax of dgetf2)
-            const unsigned long long key = avail ? (unsigned long long)__double_as_longlong(fabs(a[k])) + 1ull : 0ull;
-            const unsigned khi = (unsigned)(key >> 32), klo = (unsigned)key;
-            const unsigned mhi = __reduce_max_sync(FULL, khi);
-            const bool c1 = khi == mhi;
-            const unsigned mlo = __reduce_max_sync(FULL, c1 ? klo : 0u);
-            const unsigned ball = __ballot_sync(FULL, c1 && klo == mlo && avail);
-            const int pl = ball ? (__ffs(ball) - 1) : 0;
-            pls[k] = pl;
-            double *row = pb + (k & 1) * PLD;
+            int pl = k;
+            if (PIVOT) {   // argmax |a[k]| over the available rows (idamax of dgetf2)
+                const unsigned long long key = avail ? (unsigned long long)__double_as_longlong(fabs(a[k])) + 1ull : 0ull;
+                const unsigned khi = (unsigned)(key >> 32), klo = (unsigned)key;
+                const unsigned mhi = __reduce_max_sync(FULL, khi);
+                const bool c1 = khi == mhi;
+                const unsigned mlo = __reduce_max_sync(FULL, c1 ? klo : 0u);
+                const unsigned ball = __ballot_sync(FULL, c1 && klo == mlo && avail);
+                pl = ball ? (__ffs(ball) - 1) : 0;
+                pls[k] = pl;
+            }
+            const int kk = k & ~1;
+            double2 *row2 = reinterpret_cast<double2 *>(pb + (k & 1) * PLD);
             if (lane == pl) {
 #pragma unroll
-                for (int j = k; j < NC; ++j)
-                    if (j < n) row[j] = a[j];
-                row[NC] = rhs;
+                for (int j = kk; j < NC; j += 2) row2[j >> 1] = make_double2(a[j], a[j + 1]);
+                pb[(k & 1) * PLD + NC] = rhs;
             }
             __syncwarp();
-            const double inv = rcp(row[k]);
+            double pr[NC];
+#pragma unroll
+            for (int j = kk; j < NC; j += 2) {
+                const double2 v = row2[j >> 1];
+                pr[j] = v.x; pr[j + 1] = v.y;
+            }
+            const double inv = rcp(pr[k]);
             const double l = (avail && lane != pl) ? a[k] * inv : 0.0;
 #pragma unroll
-            for (int j = k + 1; j < NC; ++j)
-                if (j < n) a[j] = fma(-l, row[j], a[j]);
-            rhs = fma(-l, row[NC], rhs);
+            for (int j = k + 1; j < NC; ++j) a[j] = fma(-l, pr[j], a[j]);
+            rhs = fma(-l, pb[(k & 1) * PLD + NC], rhs);
             if (lane == pl) { avail = false; mystep = k; pinv = inv; }
         }
     }
@@ -185,6 +197,46 @@ template <int NB, bool LSPG> struct PromTiles {
     }
 };
 
+// One row of A and of R for node i (skewed index o; om / op: its neighbours), FEM/fem_burgers.py:730-752.
+struct PromRow { double a, b, c, R; };
+struct PromRowCtx {
+    const double *u, *bn, *hfs, *h6;
+    double a6, c1, ate, mu1;
+    int N, S, lgS;
+    bool has_e;
+};
+__device__ __forceinline__ PromRow prom_row(const PromRowCtx &x, int i, int o) {
+    const int om = sk(i - 1, x.S, x.lgS), op = sk(i + 1, x.S, x.lgS);
+    const double um = x.u[om], uc = x.u[o], up = x.u[op];
+    double pe = 0.0, Ge = 0.0, qL = 0.0, GL = 0.0;
+    if (i <= x.N - 2) {   // right element (i, i+1): convection (:418) and SUPG (:569-575)
+        const double sm = uc + up;
+        pe = fma(x.a6, uc, x.a6 * sm);
+        const double z = fma(sm * (up - uc), 1.0 / 6.0, -x.hfs[o]);
+        Ge = (x.c1 * rcp(fmax(fabs(sm), 2.0e-10))) * z;
+    }
+    if (i >= 1 && i <= x.N - 1) {   // left element (i-1, i)
+        const double sm = um + uc;
+        qL = fma(x.a6, uc, x.a6 * sm);
+        const double z = fma(sm * (uc - um), 1.0 / 6.0, -x.hfs[om]);
+        GL = (x.c1 * rcp(fmax(fabs(sm), 2.0e-10))) * z;
+    }
+    const double h6L = x.h6[om], h6R = x.h6[o];
+    double keL = 0.0, keR = 0.0;
+    if (x.has_e) {
+        keL = h6L > 0.0 ? x.ate / (6.0 * h6L) : 0.0;
+        keR = h6R > 0.0 ? x.ate / (6.0 * h6R) : 0.0;
+    }
+    PromRow r;
+    r.a = (h6L - keL) - qL;
+    r.c = (h6R - keR) + pe;
+    r.b = (2.0 * (h6L + h6R) + (keL + keR)) + (qL - pe);
+    r.R = fma(r.a, um, fma(r.b, uc, r.c * up)) - (x.bn[o] - GL + Ge);
+    if (i == 0) { r.a = 0.0; r.b = 1.0; r.c = 0.0; r.R = uc - x.mu1; }   // Dirichlet row (:741-742, :748)
+    if (i >= x.N) { r.a = 0.0; r.b = 0.0; r.c = 0.0; r.R = 0.0; }
+    return r;
+}
+
 template <int NB, bool LSPG, bool PHIS>
 __global__ void __launch_bounds__(PROM_MAXW * 32, 1) prom_kernel(const PromParams p) {
     constexpr int NC = NB * 8;
@@ -203,21 +255,23 @@ __global__ void __launch_bounds__(PROM_MAXW * 32, 1) prom_kernel(const PromParam
     const int t = lane & 3, g = lane >> 2;
     double *wbase = smem + lay.per_cta + warp * lay.per_warp;
     double *w_u = wbase + lay.u;
-    double *w_stage = wbase + lay.stage;
+    double *w_misc = wbase + lay.misc;
     double *w_bn = wbase + lay.bn;
     double *w_hfs = wbase + lay.hfs;
-    double *w_mat = w_u;                 // 16 x MAT_LD, over the dead U_k (+ the first words of stage)
-    double *w_q0 = w_stage + 96;         // q0 = Phi^T U_k        (32)
-    double *w_piv = w_stage + 16;        // pivot rows, 2 x (NC+2) (<= 68)
-    double *w_q = w_stage + 16;          // q after the solve     (32), over the dead pivot rows
+    double *w_mat = w_u;                 // 16 x MAT_LD, over the dead U_k (+ the first words of misc)
+    double *w_q0 = w_misc + 96;          // q0 = Phi^T U_k        (32)
+    double *w_piv = w_misc + 16;         // pivot rows, 2 x (NC+2) (<= 68)
+    double *w_q = w_misc + 16;           // q after the solve     (32), over the dead pivot rows
 
     const double At = p.At;
 
-    // ---- CTA prologue: permuted Phi and mesh constants ------------------------------------
+    // ---- CTA prologue: permuted Phi (+ 4 wrap rows) and mesh constants ---------------------
     if (PHIS) {
-        for (int idx = threadIdx.x; idx < NP * ldp; idx += blockDim.x) {
-            const int i = idx / ldp, j = idx - i * ldp;
-            s_phi[perm_row(i, S, lgS) * ldp + j] = (i < N && j < n) ? p.Phi[(size_t)i * n + j] : 0.0;
+        for (int idx = threadIdx.x; idx < (NP + 4) * ldp; idx += blockDim.x) {
+            const int r = idx / ldp, j = idx - r * ldp;
+            // row 4 s + t holds node t S + s; wrap row NP + t holds node (t+1) S (the row after run t)
+            const int i = r < NP ? ((r & 3) << lgS) + (r >> 2) : (r - NP < 3 ? (r - NP + 1) << lgS : N);
+            s_phi[idx] = (i < N && j < n) ? p.Phi[(size_t)i * n + j] : 0.0;
         }
     }
     for (int idx = threadIdx.x; idx < lay.arr; idx += blockDim.x) s_h6[idx] = 0.0;
@@ -225,25 +279,29 @@ __global__ void __launch_bounds__(PROM_MAXW * 32, 1) prom_kernel(const PromParam
     for (int e = threadIdx.x; e <= N - 2; e += blockDim.x) s_h6[sk(e, S, lgS)] = (p.X[e + 1] - p.X[e]) / 6.0;
     __syncthreads();
 
-    const double a6 = At / 6.0;
-    const double c1 = 1.5 * At;
-    const double ate = At * p.E;
-    const bool has_e = p.E != 0.0;
     // this thread's run of nodes, its Phi rows, its columns
     const int run0 = t << lgS;
     const double *phi_run = PHIS ? s_phi + t * ldp : p.Phi + (size_t)run0 * n;
     const int row_stride = PHIS ? 4 * ldp : n;
     const int ubase = t * (S + 1) + 2;                       // sk(run0 + s) = ubase + s
-    const int gR = n & 7;                                   // lane-group of the R column (its block is NB-1)
-    const bool col_last = ((NB - 1) * 8 + g) < n;            // only the last column block can be ragged
-    const double2 *stg = reinterpret_cast<const double2 *>(w_stage);
+    const int gR = n & 7;                                    // lane-group of the R column (its block is NB-1)
+    // Shared-memory Phi is padded with zero columns up to ldp; a ragged last block may still read a few
+    // words of the next row (finite values): they only reach accumulator rows / columns >= n, which
+    // nothing reads.  The global-memory path predicates instead (it must not read past the array).
+    const bool col_last = PHIS || ((NB - 1) * 8 + g) < n;
+    const int nblk = S >> 3;
+
+    PromRowCtx rc;
+    rc.u = w_u; rc.bn = w_bn; rc.hfs = w_hfs; rc.h6 = s_h6;
+    rc.a6 = At / 6.0; rc.c1 = 1.5 * At; rc.ate = At * p.E; rc.has_e = p.E != 0.0;
+    rc.N = N; rc.S = S; rc.lgS = lgS;
 
     for (;;) {
         int smp = 0;
         if (lane == 0) smp = (int)atomicAdd(p.counter, 1u);
         smp = __shfl_sync(FULL, smp, 0);
         if (smp >= p.B) break;
-        const double mu1 = p.mu1[smp];
+        rc.mu1 = p.mu1[smp];
         const double *atf = p.atf + (size_t)smp * N;
 
         // ---- per-sample forcing constants and the initial condition ---------------------
@@ -292,69 +350,40 @@ __global__ void __launch_bounds__(PROM_MAXW * 32, 1) prom_kernel(const PromParam
                         p0[b] = (cok && ok0) ? phi_run[b * 8 + g] : 0.0;
                     }
                 }
-                for (int blk = 0; blk < (S >> 3); ++blk) {
-                    // ---- one row of A and R per lane: node i = run0 + 8 blk + g -------------
-                    {
-                        const int i = run0 + (blk << 3) + g;
-                        const int o = ubase + (blk << 3) + g;
-                        const int om = sk(i - 1, S, lgS), op = sk(i + 1, S, lgS);
-                        const double um = w_u[om], uc = w_u[o], up = w_u[op];
-                        double pe = 0.0, qe = 0.0, Ge = 0.0, qL = 0.0, GL = 0.0;
-                        if (i <= N - 2) {   // right element (i, i+1): convection (:418) and SUPG (:569-575)
-                            const double sm = uc + up;
-                            const double tt = a6 * sm;
-                            pe = fma(a6, uc, tt);
-                            qe = fma(a6, up, tt);
-                            const double z = fma(sm * (up - uc), 1.0 / 6.0, -w_hfs[o]);
-                            Ge = (c1 * rcp(fmax(fabs(sm), 2.0e-10))) * z;
-                        }
-                        if (i >= 1 && i <= N - 1) {   // left element (i-1, i)
-                            const double sm = um + uc;
-                            qL = fma(a6, uc, a6 * sm);
-                            const double z = fma(sm * (uc - um), 1.0 / 6.0, -w_hfs[om]);
-                            GL = (c1 * rcp(fmax(fabs(sm), 2.0e-10))) * z;
-                        }
-                        (void)qe;
-                        const double h6L = s_h6[om], h6R = s_h6[o];
-                        double keL = 0.0, keR = 0.0;
-                        if (has_e) {
-                            keL = h6L > 0.0 ? ate / (6.0 * h6L) : 0.0;
-                            keR = h6R > 0.0 ? ate / (6.0 * h6R) : 0.0;
-                        }
-                        double a = (h6L - keL) - qL;
-                        double c = (h6R - keR) + pe;
-                        double b = (2.0 * (h6L + h6R) + (keL + keR)) + (qL - pe);
-                        double R = fma(a, um, fma(b, uc, c * up)) - (w_bn[o] - GL + Ge);
-                        if (i == 0) { a = 0.0; b = 1.0; c = 0.0; R = uc - mu1; }   // Dirichlet row (:741-742, :748)
-                        if (i >= N) { a = 0.0; b = 0.0; c = 0.0; R = 0.0; }
-                        double2 *dst = reinterpret_cast<double2 *>(w_stage) + 2 * lane;
-                        dst[0] = make_double2(a, b);
-                        dst[1] = make_double2(c, R);
-                    }
-                    __syncwarp();
+                // rows are assembled one block (8 nodes per k-lane) ahead, ONE node per lane
+                // (node run0 + 8 blk + g), and handed to the k-lanes by shuffles
+                PromRow nxt = prom_row(rc, run0 + g, ubase + g);
+                for (int blk = 0; blk < nblk; ++blk) {
+                    const PromRow cur = nxt;
+                    if (blk + 1 < nblk) nxt = prom_row(rc, run0 + ((blk + 1) << 3) + g, ubase + ((blk + 1) << 3) + g);
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
                         const int s = (blk << 3) + j;
-                        // Phi row of node run0 + s + 1 (the next run's first row at the end of this one)
-                        const bool inrun = s + 1 < S;
-                        const double *rp = inrun ? phi_run + (size_t)(s + 1) * row_stride
-                                           : PHIS ? s_phi + (t < 3 ? t + 1 : 0) * ldp
-                                                  : p.Phi + (size_t)(run0 + S < N ? run0 + S : 0) * n;
-                        const bool rowok = inrun ? (PHIS || run0 + s + 1 < N) : (t < 3 && (PHIS || run0 + S < N));
+                        // Phi row of node run0 + s + 1 (wrap rows make the end of a run uniform)
+                        if (PHIS) {
+                            const double *rp = phi_run + (size_t)(s + 1) * row_stride;
 #pragma unroll
-                        for (int b = 0; b < NB; ++b) {
-                            const bool cok = (b < NB - 1) || col_last;
-                            pp[b] = (cok && rowok) ? rp[b * 8 + g] : 0.0;
+                            for (int b = 0; b < NB; ++b) pp[b] = rp[b * 8 + g];
+                        } else {
+                            const int inx = run0 + s + 1;
+                            const double *rp = p.Phi + (size_t)(inx < N ? inx : 0) * n;
+#pragma unroll
+                            for (int b = 0; b < NB; ++b) {
+                                const bool cok = (b < NB - 1) || col_last;
+                                pp[b] = (cok && inx < N) ? rp[b * 8 + g] : 0.0;
+                            }
                         }
-                        const double2 ab = stg[2 * (4 * j + t)], cr = stg[2 * (4 * j + t) + 1];
+                        const int src = 4 * j + t;
+                        const double ra = shfl_idx(cur.a, src), rb = shfl_idx(cur.b, src);
+                        const double rcc = shfl_idx(cur.c, src), rR = shfl_idx(cur.R, src);
                         const double uk = w_u[ubase + s];
                         double jp[NB];
 #pragma unroll
                         for (int b = 0; b < NB; ++b) {
-                            jp[b] = fma(ab.x, pm[b], fma(ab.y, p0[b], cr.x * pp[b]));
+                            jp[b] = fma(ra, pm[b], fma(rb, p0[b], rcc * pp[b]));
                             pq[b] = fma(p0[b], uk, pq[b]);
                         }
-                        if (g == gR) jp[NB - 1] = cr.y;   // R rides as column n (block jR == NB-1)
+                        if (g == gR) jp[NB - 1] = rR;   // R rides as column n (block NB-1)
 #pragma unroll
                         for (int I = 0; I < NB; ++I) {
 #pragma unroll
@@ -366,7 +395,6 @@ __global__ void __launch_bounds__(PROM_MAXW * 32, 1) prom_kernel(const PromParam
 #pragma unroll
                         for (int b = 0; b < NB; ++b) { pm[b] = p0[b]; p0[b] = pp[b]; }
                     }
-                    __syncwarp();
                 }
                 // q0 partials: reduce over t (lanes differing in bits 0, 1)
 #pragma unroll
@@ -403,18 +431,16 @@ __global__ void __launch_bounds__(PROM_MAXW * 32, 1) prom_kernel(const PromParam
                         }
                     }
                     __syncwarp();
-                    const bool mine = (lane >> 4) == pass;
-                    const double *mr = w_mat + (lane & 15) * MAT_LD;
+                    if (pass == 0 || lane >= 16) {
+                        const double *mr = w_mat + (lane & 15) * MAT_LD;
 #pragma unroll
-                    for (int j = 0; j < NC; ++j) {
-                        const double v = (mine && lane < n && j < n) ? mr[j] : 0.0;
-                        a[j] = (pass == 0 || mine) ? v : a[j];
+                        for (int j = 0; j < NC; ++j) a[j] = mr[j];
+                        rhs = -mr[n];
                     }
-                    if (mine && lane < n) rhs = -mr[n];
                 }
                 const double q0 = (lane < n) ? w_q0[lane] : 0.0;
                 __syncwarp();
-                const double dq = lu_solve_rows<NC>(a, rhs, n, lane, w_piv);
+                const double dq = lu_solve_rows<NC, !LSPG>(a, rhs, n, lane, w_piv);
                 const double q = (lane < n) ? q0 + dq : 0.0;
                 const double sd = warp_sum((lane < n) ? dq * dq : 0.0);
                 const double sq = warp_sum(q * q);
@@ -428,8 +454,8 @@ __global__ void __launch_bounds__(PROM_MAXW * 32, 1) prom_kernel(const PromParam
                 {
                     double qv[NB];
 #pragma unroll
-                    for (int b = 0; b < NB; ++b) qv[b] = w_q[b * 8 + g];
-                    for (int blk = 0; blk < (S >> 3); ++blk) {
+                    for (int b = 0; b < NB; ++b) qv[b] = w_q[b * 8 + g];   // zero for columns >= n
+                    for (int blk = 0; blk < nblk; ++blk) {
                         double v[8];
 #pragma unroll
                         for (int j = 0; j < 8; ++j) {
