@@ -34,6 +34,9 @@ SIGNATURES = {
     "bx_prom_workspace_bytes": (c_longlong, [c_int, c_int]),
     "bx_prom_trajectories": (c_int, [c_int, c_int, c_int, c_int, P, P, c_int, P, P, c_double, c_double,
                                      P, c_int, c_double, c_int, P, P, P, P]),
+    "bx_qm_workspace_bytes": (c_longlong, [c_int, c_int, c_int]),
+    "bx_qm_prom_trajectories": (c_int, [c_int, c_int, c_int, c_int, P, P, c_int, P, P, c_double, c_double,
+                                        P, P, c_int, c_double, c_int, P, P, P, P]),
     "bx_gram_workspace_bytes": (c_longlong, [c_int, c_longlong]),
     "bx_gram_accumulate": (c_int, [c_int, c_longlong, P, P, c_int, P, P]),
 }

@@ -281,6 +281,37 @@ class FEMBurgers:
                    "bx_prom_trajectories")
         return U, iters
 
+    def pod_quadratic_manifold_batch(self, At, nTimeSteps, u0, uxa, E, mu2, Phi, H, projection="LSPG", out=None,
+                                     iters_out=None, newton_tol=1e-6, newton_itmax=25):
+        """pod_quadratic_manifold (FEM/fem_burgers.py:1081) for B samples: uxa, mu2 (B,), Phi (N, n) and
+        H (N, n(n+1)/2) shared.  Returns U (B, nTimeSteps+1, N) and iters (B, nTimeSteps) int32, CUDA tensors."""
+        pl = str(projection).lower()   # the reference compares projection.lower() (:1150-1158)
+        if pl == "galerkin":
+            code = _lib.BX_GALERKIN
+        elif pl == "lspg":
+            code = _lib.BX_LSPG
+        else:
+            raise ValueError("projection must be 'Galerkin' or 'LSPG'")
+        uxa, mu2, u0, batched, B, N, nT, U, iters = self._sweep_args(u0, uxa, mu2, nTimeSteps, out, iters_out)
+        Phi = self._dev(Phi)
+        H = self._dev(H)
+        if Phi.dim() != 2 or Phi.shape[0] != N:
+            raise ValueError("Phi must have shape (N, n)")
+        n = int(Phi.shape[1])
+        if H.dim() != 2 or H.shape[0] != N or H.shape[1] != n * (n + 1) // 2:
+            raise ValueError("H must have shape (N, n(n+1)/2)")   # quadratic_prom_simulation.py:38
+        if B == 0:
+            return U, iters
+        lib = _lib.load()
+        need = int(lib.bx_qm_workspace_bytes(B, N, n))
+        if need < 0:
+            raise _lib.BurgersB200Error("bx_qm_workspace_bytes failed: " + lib.bx_last_error().decode())
+        _lib.check(lib.bx_qm_prom_trajectories(B, N, n, nT, _ptr(self.Xd), _ptr(u0), batched, _ptr(uxa), _ptr(mu2),
+                                               float(At), float(E), _ptr(Phi), _ptr(H), code, float(newton_tol),
+                                               int(newton_itmax), _ptr(U), _ptr(iters), _ptr(self._scratch(need)),
+                                               _stream()), "bx_qm_prom_trajectories")
+        return U, iters
+
     # ------------------------------------------------------------------ legacy surface (numpy / scipy in-out)
     def _csc(self, bands):
         import scipy.sparse as sp  # return type of the reference (:353); not used for any arithmetic here
@@ -324,6 +355,16 @@ class FEMBurgers:
         """Drop-in for FEMBurgers.pod_prom_burgers (:709-785): returns ndarray (N, nTimeSteps+1)."""
         U, it = self.pod_prom_burgers_batch(At, nTimeSteps, np.asarray(u0, dtype=np.float64), [float(mu1)], E,
                                             [float(mu2)], np.asarray(Phi, dtype=np.float64), projection)
+        self.last_iters = it[0].cpu().numpy()
+        return np.ascontiguousarray(U[0].cpu().numpy().T)
+
+    def pod_quadratic_manifold(self, At, nTimeSteps, u0, uxa, E, mu2, Phi, H, projection="LSPG",
+                               newton_tol=1e-6, newton_itmax=25):
+        """Drop-in for FEMBurgers.pod_quadratic_manifold (:1081-1175): returns ndarray (N, nTimeSteps+1)."""
+        U, it = self.pod_quadratic_manifold_batch(At, nTimeSteps, np.asarray(u0, dtype=np.float64), [float(uxa)], E,
+                                                  [float(mu2)], np.asarray(Phi, dtype=np.float64),
+                                                  np.asarray(H, dtype=np.float64), projection,
+                                                  newton_tol=newton_tol, newton_itmax=newton_itmax)
         self.last_iters = it[0].cpu().numpy()
         return np.ascontiguousarray(U[0].cpu().numpy().T)
 

@@ -103,6 +103,21 @@ int bx_prom_trajectories(int B, int N, int n, int nsteps, const double *X, const
                          const double *Phi, int projection, double tol, int kmax,
                          double *U, int *iters, void *workspace, void *stream);
 
+/* FEMBurgers.pod_quadratic_manifold, FEM/fem_burgers.py:1081-1175, for B samples at once.
+ * Decoder u = Phi q + H sym(q x q), tangent Phi + H dQ/dq (get_single_Q / get_dQ_dq, :275-312; monomial
+ * order i outer, j >= i inner).  Phi: (N, n), H: (N, n(n+1)/2), both row-major, shared by all samples.
+ * uxa: (B,) left Dirichlet value per sample (the reference's scalar `uxa`; the drivers pass mu1).
+ * No SUPG term (:1141); q accumulates over the Gauss-Newton iterations and is re-projected from the full
+ * state at every time step (:1129); stops when |dq| / max(1e-14, |q|) < tol (strict, :1165-1169) or after
+ * itmax iterations; iters[b][step] = iterations executed.  projection: BX_GALERKIN / BX_LSPG, anything
+ * else BX_ERR_PROJECTION (ValueError, :1158).  1 <= n <= 31 in this build.
+ * workspace: bx_qm_workspace_bytes(B, N, n) bytes, 16-byte aligned, contents ignored.               */
+long long bx_qm_workspace_bytes(int B, int N, int n);
+int bx_qm_prom_trajectories(int B, int N, int n, int nsteps, const double *X, const double *u0,
+                            int u0_batched, const double *uxa, const double *mu2, double At, double E,
+                            const double *Phi, const double *H, int projection, double tol, int itmax,
+                            double *U, int *iters, void *workspace, void *stream);
+
 /* FEMBurgers.fom_burgers_newton AS CODED, FEM/fem_burgers.py:584-643, for B samples at once.
  * At :616 `At * dC_dU @ U0` is a matrix-vector product whose result numpy broadcasts onto every row:
  * J = T + 1 w^T, T = M + At E K + At C(U_k), w = At dC_dU U_k, row 0 <- e0^T (:619-620).  Solved exactly

@@ -1,0 +1,96 @@
+"""GPU parity of the quadratic-manifold PROM trajectory kernel (through the C ABI) against the
+reference-run golden vectors (tests/golden/qm_short.npz, made by running the unmodified reference), the
+reference's stored quadratic_rom_solutions fixtures, and the oracle on other inputs.
+Tolerance (north_star): per-time-step relative L2 <= 1e-10 in FP64, identical iteration counts; the
+500-step stored-fixture comparison uses 1e-8 because the LSPG reduced system has kappa ~ 1e8."""
+import numpy as np
+import pytest
+
+from conftest import rel_l2_per_step, GOLDEN
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-10
+
+
+@pytest.fixture(scope="module")
+def fem512(oracle):
+    import burgers_b200
+    X, T = oracle.mesh(512)
+    return burgers_b200.FEMBurgers(X, T)
+
+
+@pytest.fixture(scope="module")
+def basis():
+    return np.load(f"{GOLDEN}/qm_Phi.npy"), np.load(f"{GOLDEN}/qm_H.npy")
+
+
+@pytest.mark.parametrize("proj", ["LSPG", "Galerkin"])
+def test_legacy_qm_vs_reference_run(proj, golden, fem512, basis):
+    g = golden("qm_short.npz")
+    Phi, H = basis
+    U = fem512.pod_quadratic_manifold(0.05, 6, np.ones(512), 4.75, 0.0, 0.02, Phi, H, proj)
+    assert U.shape == (512, 7) and U.dtype == np.float64
+    assert np.array_equal(fem512.last_iters, g[f"it_{proj}"])
+    assert rel_l2_per_step(U, g[f"U_{proj}"]) <= TOL
+
+
+def test_projection_spelling_and_errors(fem512, basis):
+    Phi, H = basis
+    # the reference lower-cases the projection name (:1150-1158)
+    U1 = fem512.pod_quadratic_manifold(0.05, 2, np.ones(512), 4.75, 0.0, 0.02, Phi, H, "lspg")
+    U2 = fem512.pod_quadratic_manifold(0.05, 2, np.ones(512), 4.75, 0.0, 0.02, Phi, H, "LSPG")
+    assert np.array_equal(U1, U2)
+    with pytest.raises(ValueError, match="projection must be"):
+        fem512.pod_quadratic_manifold(0.05, 1, np.ones(512), 4.75, 0.0, 0.02, Phi, H, "POD")
+    with pytest.raises(ValueError):
+        fem512.pod_quadratic_manifold(0.05, 1, np.ones(512), 4.75, 0.0, 0.02, Phi, H[:, :-1], "LSPG")
+
+
+@pytest.mark.parametrize("name", ["quadratic_PROM_U_PROM_21_modes_mu1_4.560_mu2_0.0190",
+                                  "quadratic_PROM_U_PROM_21_modes_mu1_4.750_mu2_0.0200",
+                                  "quadratic_PROM_U_PROM_21_modes_mu1_5.190_mu2_0.0260"])
+def test_stored_fixture_full_500_steps(name, golden, fem512, basis):
+    g = golden("qm_fixtures.npz")
+    Phi, H = basis
+    parts = name.split("_")
+    mu1, mu2 = float(parts[7]), float(parts[9])
+    U = fem512.pod_quadratic_manifold(0.05, 500, np.ones(512), mu1, 0.0, mu2, Phi, H, "LSPG")
+    assert rel_l2_per_step(U[:, g["steps"]], g[name]) <= 1e-8
+
+
+@pytest.mark.parametrize("proj", ["LSPG", "Galerkin"])
+def test_batch_vs_oracle(proj, oracle, fem512, basis):
+    """a batch of samples, non-default tolerance / iteration cap (cap reached on some steps)"""
+    Phi, H = basis
+    X, _ = oracle.mesh(512)
+    mu1 = np.array([4.3, 4.75, 5.4, 4.9, 5.1]); mu2 = np.array([0.016, 0.02, 0.029, 0.024, 0.018])
+    U, it = fem512.pod_quadratic_manifold_batch(0.05, 5, np.ones(512), mu1, 0.0, mu2, Phi, H, proj,
+                                                newton_tol=1e-7, newton_itmax=9)
+    U = U.cpu().numpy(); it = it.cpu().numpy()
+    for b in range(mu1.size):
+        Uo, ito = oracle.pod_quadratic_manifold(X, 0.05, 5, np.ones(512), mu1[b], 0.0, mu2[b], Phi, H, proj,
+                                                newton_tol=1e-7, newton_itmax=9)
+        assert np.array_equal(it[b], ito), (b, it[b], ito)
+        assert rel_l2_per_step(U[b].T, Uo) <= TOL
+
+
+def test_small_mesh_small_basis(oracle):
+    """N = 100 (not a multiple of 4 S), n = 5, non-uniform mesh, E != 0: H from a ridge fit of oracle snapshots."""
+    import burgers_b200
+    rng = np.random.default_rng(3)
+    X = np.sort(np.concatenate([[0.0, 100.0], 100.0 * rng.random(98)]))
+    N, n = X.size, 5
+    Us, _ = oracle.fom_burgers_batch(X, 0.05, 30, np.ones(N), np.array([4.4, 5.2]), 0.01, np.array([0.017, 0.027]))
+    S = Us.reshape(-1, N).T
+    Phi = np.linalg.svd(S, full_matrices=False)[0][:, :n].copy()
+    q = Phi.T @ S
+    iu, ju = np.triu_indices(n)
+    Q = q[iu] * q[ju]
+    Em = S - Phi @ q
+    H = np.linalg.solve(Q @ Q.T + 1e-2 * np.eye(Q.shape[0]), Q @ Em.T).T.copy()
+    fem = burgers_b200.FEMBurgers(X)
+    for proj in ("LSPG", "Galerkin"):
+        U = fem.pod_quadratic_manifold(0.05, 6, np.ones(N), 4.8, 0.01, 0.02, Phi, H, proj)
+        Uo, ito = oracle.pod_quadratic_manifold(X, 0.05, 6, np.ones(N), 4.8, 0.01, 0.02, Phi, H, proj)
+        assert np.array_equal(fem.last_iters, ito)
+        assert rel_l2_per_step(U, Uo) <= TOL
