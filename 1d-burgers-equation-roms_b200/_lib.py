@@ -29,6 +29,9 @@ SIGNATURES = {
     "bx_workspace_bytes": (c_longlong, []),
     "bx_fom_picard_trajectories": (c_int, [c_int, c_int, c_int, P, P, c_int, P, P, c_double, c_double,
                                            c_double, c_int, P, P, P, P]),
+    "bx_fine_workspace_bytes": (c_longlong, [c_int]),
+    "bx_fom_picard_finemesh": (c_int, [c_int, c_int, c_int, P, P, c_int, P, P, c_double, c_double,
+                                       c_double, c_int, P, P, P, P]),
     "bx_fom_newton_trajectories": (c_int, [c_int, c_int, c_int, P, P, c_int, P, P, c_double, c_double,
                                            c_double, c_double, c_int, P, P, P, P]),
     "bx_prom_workspace_bytes": (c_longlong, [c_int, c_int]),

@@ -1,0 +1,476 @@
+// bx_fine.cu — fine-mesh FOM trajectory: FEMBurgers.fom_burgers (FEM/fem_burgers.py:646-707) for a
+// mesh far larger than one warp can hold (BASELINE config 5: 2^20 nodes, one trajectory).
+//
+// ONE persistent cooperative kernel integrates the whole trajectory.  The mesh is cut into
+// contiguous partitions three levels deep — 16 nodes per thread, 32 threads per warp, 16 warps per
+// CTA (8192 nodes), G = ceil(N / 8192) CTAs — and each Picard iteration solves the N x N tridiagonal
+// system A delta = -R by a partition (SPIKE / cyclic-reduction type) method on that hierarchy:
+//   thread  assembles its 16 rows from the closed forms of the 2-point-Gauss element integrals
+//           (as bx_fom.cu), sweeps them in continuant form carrying the coupling to the previous
+//           partition's last unknown P, and condenses to
+//              row:  al P + be x_last + ga E = rho      (E = first unknown of the next partition)
+//              fgr:  x_first = R - F P - G x_last
+//   warp / CTA   "group_up": neighbours' fgr close the interior couplings (E -> x_last of the next
+//           partition), a 32-lane parallel cyclic reduction with three right-hand sides solves the
+//           group's rows for  x_last(j) = y_j - P z1_j + X z2_j  (P, X: the group's own boundary
+//           unknowns), and the group's row / fgr follow by substitution;
+//   grid    every CTA publishes one row + fgr (7 doubles); after a grid barrier each CTA solves the
+//           G-row closed system redundantly (5 rows per lane + warp PCR) and walks back down.
+// Then local back-substitution, update, |delta|^2 and |U|^2; a second grid barrier carries the norm
+// partials (summed in CTA order: every CTA takes the same decision) and the partition-edge states.
+// U_k lives in registers and the swept rows (cs, rs, fs) in shared memory (192 KB) for the whole
+// trajectory; mesh / forcing constants and M U^n + At F stream from an L2-resident scratch in a
+// [row][thread] interleaved layout (coalesced).  HBM traffic: the 8N-byte snapshot per time step.
+#include "bx_common.cuh"
+#include <cstdint>
+
+namespace bx {
+
+constexpr int FM = 16;            // nodes per thread
+constexpr int FT = 512;           // threads per CTA
+constexpr int FW = FT / 32;       // warps per CTA
+constexpr int FNODES = FM * FT;   // nodes per CTA
+constexpr int FGMAX = 160;        // CTAs the top-level solve covers (5 rows per lane)
+
+struct FineParams {
+    int B, N, nsteps, kmax, G;
+    const double *X;
+    const double *u0;
+    long long u0_stride;
+    const double *mu1;
+    const double *mu2;
+    double At, E, tol2;
+    double *U;
+    int *iters;
+    double *g_h6, *g_hfs;     // (FM+1) x FT per CTA, element jj at [(jj+1) * FT + tid]
+    double *g_atf, *g_bn;     // FM x FT per CTA, node j at [j * FT + tid]
+    double *g_rows;           // [G][8]: al, be, gaE, rho, F, G, R, -
+    double *g_norm;           // [G][4]: sd, su, u_first, u_last
+    unsigned int *bar;
+};
+
+struct Lvl { double y, z1, z2; };
+
+__device__ __forceinline__ void warp_sum_pair(double &a, double &b) {
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) { a += shfl_xor(a, s); b += shfl_xor(b, s); }
+}
+
+// one division-free PCR step on a row with three right-hand sides (see pcr_step in bx_common.cuh)
+__device__ __forceinline__ void pcr_step3(double &al, double &be, double &ga, double &r0, double &r1, double &r2, int s) {
+    const double al_m = shfl_up(al, s), be_m = shfl_up(be, s), ga_m = shfl_up(ga, s);
+    const double al_p = shfl_down(al, s), be_p = shfl_down(be, s), ga_p = shfl_down(ga, s);
+    const double r0m = shfl_up(r0, s), r1m = shfl_up(r1, s), r2m = shfl_up(r2, s);
+    const double r0p = shfl_down(r0, s), r1p = shfl_down(r1, s), r2p = shfl_down(r2, s);
+    const double bb = be_m * be_p, ab = al * be_p, gb = ga * be_m;
+    be = fma(be, bb, -fma(ab, ga_m, gb * al_p));
+    r0 = fma(r0, bb, -fma(ab, r0m, gb * r0p));
+    r1 = fma(r1, bb, -fma(ab, r1m, gb * r1p));
+    r2 = fma(r2, bb, -fma(ab, r2m, gb * r2p));
+    al = -ab * al_m;
+    ga = -gb * ga_p;
+}
+
+// Group m (<= 32) consecutive partitions, one per lane (lanes >= m must hold identity rows:
+// al = ga = 0, be = 1, rho = 0, F = G = R = 0).  In: the lane's row (al, be, gaE, rho) and fgr.
+// Out: lv (x_last(lane) = y - P z1 + X z2) and, valid on EVERY lane, the group's row and fgr.
+__device__ __forceinline__ Lvl group_up(int m, int lane, double &al, double &be, double &ga, double &rho,
+                                        double &F, double &G, double &R) {
+    // close the interior couplings with the next partition's fgr
+    const double Fn = shfl_down(F, 1), Gn = shfl_down(G, 1), Rn = shfl_down(R, 1);
+    const bool last = lane == m - 1;
+    const double gaE = ga;
+    double a_ = al, b_ = be, g_ = 0.0, r0 = rho, r1 = 0.0, r2 = 0.0;
+    if (lane < m - 1) {
+        b_ = fma(-gaE, Fn, be);
+        g_ = -gaE * Gn;
+        r0 = fma(-gaE, Rn, rho);
+    }
+    if (lane == 0) { r1 = a_; a_ = 0.0; }                    // coupling to the group's P moves to the right
+    if (last) { a_ = 0.0; b_ = 1.0; g_ = 0.0; r0 = 0.0; r1 = 0.0; r2 = 1.0; }   // x_last(m-1) = X
+    if (lane >= m) { a_ = 0.0; b_ = 1.0; g_ = 0.0; r0 = 0.0; r1 = 0.0; r2 = 0.0; }
+    pcr_step3(a_, b_, g_, r0, r1, r2, 1);
+    pcr_step3(a_, b_, g_, r0, r1, r2, 2);
+    {
+        const double inv = rcp(b_);
+        a_ *= inv; g_ *= inv; r0 *= inv; r1 *= inv; r2 *= inv; b_ = 1.0;
+    }
+    pcr_step3(a_, b_, g_, r0, r1, r2, 4);
+    pcr_step3(a_, b_, g_, r0, r1, r2, 8);
+    pcr_step3(a_, b_, g_, r0, r1, r2, 16);
+    const double inv = rcp(b_);
+    Lvl lv;
+    lv.y = r0 * inv; lv.z1 = r1 * inv; lv.z2 = r2 * inv;
+    // the group's row: the true last row with x_last(m-2) substituted (lane -1 stands for P itself)
+    double ym = shfl_up(lv.y, 1), z1m = shfl_up(lv.z1, 1), z2m = shfl_up(lv.z2, 1);
+    if (m == 1) { ym = 0.0; z1m = -1.0; z2m = 0.0; }
+    const double gal = -al * z1m, gbe = fma(al, z2m, be), grho = fma(-al, ym, rho);
+    // the group's fgr from partition 0
+    const double gF = fma(-G, lv.z1, F), gG = G * lv.z2, gR = fma(-G, lv.y, R);
+    al = shfl_idx(gal, m - 1); be = shfl_idx(gbe, m - 1); ga = shfl_idx(gaE, m - 1); rho = shfl_idx(grho, m - 1);
+    F = shfl_idx(gF, 0); G = shfl_idx(gG, 0); R = shfl_idx(gR, 0);
+    return lv;
+}
+
+// all CTAs of the (co-resident, cooperative) grid; monotonic counter, target = epoch * G
+__device__ __forceinline__ void grid_barrier(unsigned int *bar, unsigned int G, unsigned int &epoch) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        ++epoch;
+        __threadfence();
+        atomicAdd(bar, 1u);
+        const unsigned int target = epoch * G;
+        unsigned int v;
+        do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(bar) : "memory");
+        } while (v < target);
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(FT, 1) fine_fom_kernel(const FineParams p) {
+    extern __shared__ __align__(16) double smem[];
+    double *s_cs = smem;                    // swept rows of this thread: [j * FT + tid]
+    double *s_rs = s_cs + FNODES;
+    double *s_fs = s_rs + FNODES;
+    double *s_x = s_fs + FNODES;            // small exchange area (256 doubles)
+    double *s_wrow = s_x;                   // [FW][8] warp rows + fgr
+    double *s_top = s_x + 8 * FW;           // [FGMAX + 1]: x_last of CTA c at [c + 1], [0] = 0
+    double *s_wx = s_top + FGMAX + 2;       // [FW + 1]: x_last of warp w at [w + 1], [0] = CTA's P
+    double *s_red = s_wx + FW + 2;          // [FW][4] norm partials / warp edge states
+    double *s_dec = s_red + 4 * FW;         // [4]: sd, su, uL of the CTA, uR of the CTA
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int cta = blockIdx.x, G = p.G, N = p.N;
+    const int node0 = (cta * FT + tid) * FM;
+    const int jl = N - 1 - node0;           // local index of the last real row (may be outside [0, FM))
+    const double At = p.At;
+    const double a6 = At / 6.0, c1 = 1.5 * At;
+    const bool has_e = p.E != 0.0;
+    const double ate = At * p.E;
+    unsigned int epoch = 0;
+
+    double *t_h6 = p.g_h6 + (size_t)cta * (FM + 1) * FT + tid;
+    double *t_hfs = p.g_hfs + (size_t)cta * (FM + 1) * FT + tid;
+    double *t_atf = p.g_atf + (size_t)cta * FNODES + tid;
+    double *t_bn = p.g_bn + (size_t)cta * FNODES + tid;
+    double *t_cs = s_cs + tid, *t_rs = s_rs + tid, *t_fs = s_fs + tid;
+
+    // ---- mesh constants of this thread's elements (jj = -1 .. FM-1), once ----------------------
+    for (int jj = -1; jj < FM; ++jj) {
+        const int e = node0 + jj;
+        double h6 = 0.0;
+        if (e >= 0 && e <= N - 2) h6 = (p.X[e + 1] - p.X[e]) / 6.0;
+        t_h6[(jj + 1) * FT] = h6;
+    }
+
+    const bool leftv = node0 > 0 && jl >= 0;
+    const double a6L = leftv ? a6 : 0.0, c1L = leftv ? c1 : 0.0;
+
+    for (int smp = 0; smp < p.B; ++smp) {
+        const double mu1 = p.mu1[smp], mu2 = p.mu2[smp];
+        // ---- per-sample forcing constants (FEM/fem_burgers.py:449-455, 565) ---------------------
+        {
+            double left = 0.0;
+            for (int jj = -1; jj < FM; ++jj) {
+                const int e = node0 + jj;
+                double hfs = 0.0, c0 = 0.0, cr = 0.0;
+                if (e >= 0 && e <= N - 2) {
+                    const double x1 = p.X[e], x2 = p.X[e + 1];
+                    const double f1 = 0.02 * exp(mu2 * (BX_GA * x1 + BX_GB * x2));
+                    const double f2 = 0.02 * exp(mu2 * (BX_GB * x1 + BX_GA * x2));
+                    const double dV = 0.5 * (x2 - x1);
+                    hfs = ((x2 - x1) / 6.0) * (f1 + f2);
+                    c0 = (f1 * BX_GA + f2 * BX_GB) * dV;
+                    cr = (f1 * BX_GB + f2 * BX_GA) * dV;
+                }
+                t_hfs[(jj + 1) * FT] = hfs;
+                if (jj >= 0) t_atf[jj * FT] = At * (left + c0);
+                left = cr;
+            }
+        }
+        // ---- initial condition -> registers + snapshot 0 ---------------------------------------
+        double u[FM];
+        double *Us = p.U + (long long)smp * (long long)(p.nsteps + 1) * N;
+        {
+            const double *u0p = p.u0 + (long long)smp * p.u0_stride;
+#pragma unroll
+            for (int j = 0; j < FM; ++j) {
+                u[j] = (node0 + j < N) ? u0p[node0 + j] : 0.0;
+                if (node0 + j < N) Us[node0 + j] = u[j];
+            }
+        }
+        double sd = 0.0, su = 0.0, uL = 0.0, uR = 0.0;
+
+        // publish partition-edge states (and norm partials), grid barrier, fetch neighbours' edges and
+        // the grid-wide norms (summed in CTA order)
+        auto exchange = [&](double psd, double psu) {
+            warp_sum_pair(psd, psu);
+            if (lane == 0) { s_red[4 * warp + 0] = psd; s_red[4 * warp + 1] = psu; s_red[4 * warp + 2] = u[0]; }
+            if (lane == 31) s_red[4 * warp + 3] = u[FM - 1];
+            __syncthreads();
+            if (tid == 0) {
+                double a = 0.0, b = 0.0;
+                for (int w = 0; w < FW; ++w) { a += s_red[4 * w]; b += s_red[4 * w + 1]; }
+                double *gn = p.g_norm + 4 * cta;
+                gn[0] = a; gn[1] = b; gn[2] = s_red[2]; gn[3] = s_red[4 * (FW - 1) + 3];
+            }
+            grid_barrier(p.bar, (unsigned)G, epoch);
+            if (warp == 0) {
+                // sum of G partials, fixed order: lane l takes CTAs 5 l .. 5 l + 4, then a butterfly
+                double a = 0.0, b = 0.0;
+                for (int c = 5 * lane; c < 5 * lane + 5 && c < G; ++c) {
+                    a += __ldcg(p.g_norm + 4 * c); b += __ldcg(p.g_norm + 4 * c + 1);
+                }
+                warp_sum_pair(a, b);
+                if (lane == 0) {
+                    s_dec[0] = a; s_dec[1] = b;
+                    s_dec[2] = cta > 0 ? __ldcg(p.g_norm + 4 * (cta - 1) + 3) : 0.0;
+                    s_dec[3] = cta < G - 1 ? __ldcg(p.g_norm + 4 * (cta + 1) + 2) : 0.0;
+                }
+            }
+            __syncthreads();
+            sd = s_dec[0]; su = s_dec[1];
+            uL = shfl_up(u[FM - 1], 1);
+            uR = shfl_down(u[0], 1);
+            if (lane == 0) uL = warp > 0 ? s_red[4 * (warp - 1) + 3] : s_dec[2];
+            if (lane == 31) uR = warp < FW - 1 ? s_red[4 * (warp + 1) + 2] : s_dec[3];
+            __syncthreads();   // s_red / s_dec are rewritten by the next exchange
+        };
+        exchange(0.0, 0.0);
+
+        for (int n = 0; n < p.nsteps; ++n) {
+            // ---- bn = M U^n + At F (constant during the Picard loop, :683) ---------------------
+            {
+                double h6L = t_h6[0];
+#pragma unroll
+                for (int j = 0; j < FM; ++j) {
+                    const double h6R = t_h6[(j + 1) * FT];
+                    const double um = (j == 0) ? uL : u[j > 0 ? j - 1 : 0];
+                    const double up = (j == FM - 1) ? uR : u[j < FM - 1 ? j + 1 : j];
+                    t_bn[j * FT] = h6L * um + (2.0 * (h6L + h6R)) * u[j] + h6R * up + t_atf[j * FT];
+                    h6L = h6R;
+                }
+            }
+            int k = 0;
+            do {
+                // ================= thread level: assemble + sweep (:667-692) ======================
+                double al, be, ga, rho, F, Gc, R;
+                {
+                    Continuant<FM> ct;
+                    double h6L = t_h6[0];
+                    double qL, GL;
+                    {
+                        const double u1 = uL, u2 = u[0];
+                        const double sm = u1 + u2;
+                        qL = fma(a6L, u2, a6L * sm);
+                        const double z = fma(sm * (u2 - u1), 1.0 / 6.0, -t_hfs[0]);
+                        GL = (c1L * rcp(fmax(fabs(sm), 2.0e-10))) * z;
+                    }
+                    double csj = 0.0, rsj = 0.0, fsj = 0.0;
+#pragma unroll
+                    for (int j = 0; j < FM; ++j) {
+                        const double h6R = t_h6[(j + 1) * FT];
+                        const double um = (j == 0) ? uL : u[j > 0 ? j - 1 : 0];
+                        const double up = (j == FM - 1) ? uR : u[j < FM - 1 ? j + 1 : j];
+                        const double u1 = u[j], u2 = up;
+                        const double sm = u1 + u2;
+                        const double tt = a6 * sm;
+                        double pe = fma(a6, u1, tt);
+                        double qe = fma(a6, u2, tt);
+                        const double z = fma(sm * (u2 - u1), 1.0 / 6.0, -t_hfs[(j + 1) * FT]);
+                        double Ge = (c1 * rcp(fmax(fabs(sm), 2.0e-10))) * z;
+                        if (j >= jl) { pe = 0.0; qe = 0.0; Ge = 0.0; }   // no element to the right of node N-1
+                        double keL = 0.0, keR = 0.0;
+                        if (has_e) {
+                            keL = h6L > 0.0 ? ate / (6.0 * h6L) : 0.0;
+                            keR = h6R > 0.0 ? ate / (6.0 * h6R) : 0.0;
+                        }
+                        double a = (h6L - keL) - qL;
+                        double c = (h6R - keR) + pe;
+                        double b = (2.0 * (h6L + h6R) + (keL + keR)) + (qL - pe);
+                        double r = (t_bn[j * FT] - GL + Ge) - fma(a, um, fma(b, u1, c * u2));
+                        if (j > jl) { a = 0.0; b = 1.0; c = 0.0; r = 0.0; }              // padded row
+                        if (j == 0 && node0 == 0) { a = 0.0; b = 1.0; c = 0.0; r = mu1 - u1; }   // Dirichlet row (:679-686)
+                        ct.row(j, a, b, c, r, csj, rsj, fsj);
+                        t_cs[j * FT] = csj; t_rs[j * FT] = rsj; t_fs[j * FT] = fsj;
+                        h6L = h6R; qL = qe; GL = Ge;
+                    }
+                    // row of the last unknown, and x_first = R - F P - G x_last by an upward sweep
+                    al = fsj; be = 1.0; ga = csj; rho = rsj;
+                    F = t_fs[(FM - 2) * FT]; Gc = t_cs[(FM - 2) * FT]; R = t_rs[(FM - 2) * FT];
+#pragma unroll
+                    for (int j = FM - 3; j >= 0; --j) {
+                        const double cj = t_cs[j * FT];
+                        F = fma(-cj, F, t_fs[j * FT]);
+                        Gc = -cj * Gc;
+                        R = fma(-cj, R, t_rs[j * FT]);
+                    }
+                }
+                // ================= warp level ====================================================
+                const Lvl lw = group_up(32, lane, al, be, ga, rho, F, Gc, R);
+                if (lane == 0) {
+                    double *d = s_wrow + 8 * warp;
+                    d[0] = al; d[1] = be; d[2] = ga; d[3] = rho; d[4] = F; d[5] = Gc; d[6] = R;
+                }
+                __syncthreads();
+                // ================= CTA level (warp 0) + publish ==================================
+                Lvl lc; lc.y = 0.0; lc.z1 = 0.0; lc.z2 = 0.0;
+                if (warp == 0) {
+                    double a2 = 0.0, b2 = 1.0, g2 = 0.0, r2 = 0.0, F2 = 0.0, G2 = 0.0, R2 = 0.0;
+                    if (lane < FW) {
+                        const double *d = s_wrow + 8 * lane;
+                        a2 = d[0]; b2 = d[1]; g2 = d[2]; r2 = d[3]; F2 = d[4]; G2 = d[5]; R2 = d[6];
+                    }
+                    lc = group_up(FW, lane, a2, b2, g2, r2, F2, G2, R2);
+                    if (lane == 0) {
+                        double *d = p.g_rows + 8 * cta;
+                        d[0] = a2; d[1] = b2; d[2] = g2; d[3] = r2; d[4] = F2; d[5] = G2; d[6] = R2;
+                    }
+                }
+                grid_barrier(p.bar, (unsigned)G, epoch);
+                // ================= grid level: closed G-row system, solved by every CTA ===========
+                if (warp == 0) {
+                    constexpr int TM = FGMAX / 32;   // 5 rows per lane
+                    double cs5[TM], rs5[TM], fs5[TM];
+                    Continuant<TM> ct;
+#pragma unroll
+                    for (int j = 0; j < TM; ++j) {
+                        const int c = lane * TM + j;
+                        double a = 0.0, b = 1.0, cc = 0.0, r = 0.0;
+                        if (c < G) {
+                            const double *d = p.g_rows + 8 * c;
+                            a = __ldcg(d); b = __ldcg(d + 1); r = __ldcg(d + 3);
+                            if (c < G - 1) {   // E of CTA c = x_first of CTA c+1
+                                const double gE = __ldcg(d + 2);
+                                const double Fn = __ldcg(d + 8 + 4), Gn = __ldcg(d + 8 + 5), Rn = __ldcg(d + 8 + 6);
+                                b = fma(-gE, Fn, b); cc = -gE * Gn; r = fma(-gE, Rn, r);
+                            }
+                            if (c == 0) a = 0.0;
+                        }
+                        ct.row(j, a, b, cc, r, cs5[j], rs5[j], fs5[j]);
+                    }
+                    double xl, P;
+                    partition_condense<TM>(cs5, rs5, fs5, lane, xl, P);
+                    double x = xl;
+#pragma unroll
+                    for (int j = TM - 1; j >= 0; --j) {
+                        if (j < TM - 1) x = fma(-cs5[j], x, fma(-fs5[j], P, rs5[j]));
+                        s_top[lane * TM + j + 1] = x;
+                    }
+                    if (lane == 0) s_top[0] = 0.0;
+                    __syncwarp();
+                    // CTA level, downwards: x_last of every warp
+                    const double Pc = s_top[cta], Xc = s_top[cta + 1];
+                    if (lane < FW) s_wx[lane + 1] = fma(Xc, lc.z2, fma(-Pc, lc.z1, lc.y));
+                    if (lane == 0) s_wx[0] = Pc;
+                }
+                __syncthreads();
+                // ================= warp level, downwards; back-substitution, update, norms ========
+                double psd = 0.0, psu = 0.0;
+                {
+                    const double Pw = s_wx[warp], Xw = s_wx[warp + 1];
+                    const double xl = fma(Xw, lw.z2, fma(-Pw, lw.z1, lw.y));
+                    double P = shfl_up(xl, 1);
+                    if (lane == 0) P = Pw;
+                    double x = xl;
+#pragma unroll
+                    for (int j = FM - 1; j >= 0; --j) {
+                        if (j < FM - 1) x = fma(-t_cs[j * FT], x, fma(-t_fs[j * FT], P, t_rs[j * FT]));
+                        psd = fma(x, x, psd);
+                        u[j] += x;
+                        psu = fma(u[j], u[j], psu);
+                    }
+                }
+                exchange(psd, psu);
+                ++k;
+            } while (sd > p.tol2 * su && k < p.kmax);
+
+            // ---- snapshot n+1 (:705) and iteration count -------------------------------------------
+            double *Un1 = Us + (long long)(n + 1) * N + node0;
+            if (node0 + FM <= N && ((N & 1) == 0)) {
+#pragma unroll
+                for (int j = 0; j < FM; j += 2) *reinterpret_cast<double2 *>(Un1 + j) = make_double2(u[j], u[j + 1]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < FM; ++j) if (node0 + j < N) Un1[j] = u[j];
+            }
+            if (cta == 0 && tid == 0 && p.iters) p.iters[(long long)smp * p.nsteps + n] = k;
+        }
+    }
+}
+
+constexpr size_t FINE_SMEM = sizeof(double) * (3 * (size_t)FNODES + 512);
+
+struct FinePlan {
+    int G;
+    size_t off_h6, off_hfs, off_atf, off_bn, off_rows, off_norm, total;
+};
+
+static int fine_plan(int N, FinePlan &pl) {
+    pl.G = (N + FNODES - 1) / FNODES;
+    size_t o = 256;
+    auto take = [&](size_t doubles) { size_t at = o; o += sizeof(double) * doubles; o = (o + 255) & ~(size_t)255; return at; };
+    pl.off_h6 = take((size_t)pl.G * (FM + 1) * FT);
+    pl.off_hfs = take((size_t)pl.G * (FM + 1) * FT);
+    pl.off_atf = take((size_t)pl.G * FNODES);
+    pl.off_bn = take((size_t)pl.G * FNODES);
+    pl.off_rows = take((size_t)(pl.G + 1) * 8);
+    pl.off_norm = take((size_t)pl.G * 4);
+    pl.total = o;
+    return BX_OK;
+}
+
+}  // namespace bx
+
+extern "C" long long bx_fine_workspace_bytes(int N) {
+    using namespace bx;
+    if (N < 2) return -1;
+    FinePlan pl;
+    fine_plan(N, pl);
+    return (long long)pl.total;
+}
+
+extern "C" int bx_fom_picard_finemesh(int B, int N, int nsteps, const double *X, const double *u0, int u0_batched,
+                                      const double *mu1, const double *mu2, double At, double E, double tol,
+                                      int kmax, double *U, int *iters, void *workspace, void *stream) {
+    using namespace bx;
+    BX_REQUIRE(B >= 0 && nsteps >= 0, "B and nsteps must be non-negative");
+    BX_REQUIRE(N >= 2, "need at least 2 nodes (got N = %d)", N);
+    BX_REQUIRE(kmax >= 1, "kmax must be >= 1 (the reference loop body defines U1)");
+    if (B == 0) return BX_OK;
+    BX_REQUIRE(X && u0 && mu1 && mu2 && U && workspace, "null device pointer");
+    FinePlan pl;
+    fine_plan(N, pl);
+    int dev = 0, sms = 0, coop = 0, occ = 0;
+    BX_CUDA(cudaGetDevice(&dev));
+    BX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    BX_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
+    BX_CUDA(cudaFuncSetAttribute(fine_fom_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FINE_SMEM));
+    BX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fine_fom_kernel, FT, FINE_SMEM));
+    if (!coop || occ < 1 || pl.G > sms * occ || pl.G > FGMAX) {
+        set_error("bx_fom_picard_finemesh: N = %d needs %d co-resident CTAs of %d nodes; this device runs %d", N, pl.G,
+                  FNODES, (coop && occ >= 1) ? (sms * occ < FGMAX ? sms * occ : FGMAX) : 0);
+        return BX_ERR_UNSUPPORTED;
+    }
+    char *ws = static_cast<char *>(workspace);
+    FineParams p;
+    p.B = B; p.N = N; p.nsteps = nsteps; p.kmax = kmax; p.G = pl.G;
+    p.X = X; p.u0 = u0; p.u0_stride = u0_batched ? N : 0;
+    p.mu1 = mu1; p.mu2 = mu2; p.At = At; p.E = E; p.tol2 = tol * tol;
+    p.U = U; p.iters = iters;
+    p.bar = reinterpret_cast<unsigned int *>(ws);
+    p.g_h6 = reinterpret_cast<double *>(ws + pl.off_h6);
+    p.g_hfs = reinterpret_cast<double *>(ws + pl.off_hfs);
+    p.g_atf = reinterpret_cast<double *>(ws + pl.off_atf);
+    p.g_bn = reinterpret_cast<double *>(ws + pl.off_bn);
+    p.g_rows = reinterpret_cast<double *>(ws + pl.off_rows);
+    p.g_norm = reinterpret_cast<double *>(ws + pl.off_norm);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    BX_CUDA(cudaMemsetAsync(p.bar, 0, 256, st));
+    void *args[] = {&p};
+    BX_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void *>(fine_fom_kernel), dim3(pl.G), dim3(FT), args,
+                                        FINE_SMEM, st));
+    return BX_OK;
+}

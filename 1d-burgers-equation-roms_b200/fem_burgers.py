@@ -49,6 +49,8 @@ def validate_mesh(X, T):
 
 
 class FEMBurgers:
+    WARP_MESH_MAX = 1024   # largest mesh the one-warp-per-trajectory kernel covers
+
     def __init__(self, X, T=None, device=None):
         self.X = validate_mesh(X, T)
         self.T = T if T is not None else np.array([np.arange(1, self.X.size), np.arange(2, self.X.size + 1)]).T
@@ -210,6 +212,14 @@ class FEMBurgers:
         iters = iters_out if iters_out is not None else self._new(B, nT, dtype=torch.int32)
         lib = _lib.load()
         if B == 0:
+            return U, iters
+        if N > self.WARP_MESH_MAX:
+            # fine mesh (BASELINE config 5): persistent cooperative kernel, partition solve across CTAs
+            ws = self._scratch(int(lib.bx_fine_workspace_bytes(N)))
+            _lib.check(lib.bx_fom_picard_finemesh(B, N, nT, _ptr(self.Xd), _ptr(u0), batched, _ptr(mu1),
+                                                  _ptr(mu2), float(At), float(E), float(tol), int(kmax),
+                                                  _ptr(U), _ptr(iters), _ptr(ws), _stream()),
+                       "bx_fom_picard_finemesh")
             return U, iters
         _lib.check(lib.bx_fom_picard_trajectories(B, N, nT, _ptr(self.Xd), _ptr(u0), batched, _ptr(mu1),
                                                   _ptr(mu2), float(At), float(E), float(tol), int(kmax),

@@ -89,6 +89,17 @@ int bx_fom_picard_trajectories(int B, int N, int nsteps, const double *X, const 
                                double At, double E, double tol, int kmax,
                                double *U, int *iters, void *workspace, void *stream);
 
+/* FEMBurgers.fom_burgers, FEM/fem_burgers.py:646-707, on a mesh too large for one warp (N > 1024;
+ * BASELINE config 5: 2^20 nodes): one persistent cooperative kernel per call, the N x N tridiagonal solve
+ * of every Picard iteration done by a three-level partition / cyclic-reduction method across threads,
+ * warps and CTAs (two grid barriers per iteration), state on chip for the whole trajectory.  The B samples
+ * are integrated one after the other.  Same arguments and outputs as bx_fom_picard_trajectories.
+ * N <= 8192 * min(SM count, 160).  workspace: bx_fine_workspace_bytes(N) bytes, contents ignored.       */
+long long bx_fine_workspace_bytes(int N);
+int bx_fom_picard_finemesh(int B, int N, int nsteps, const double *X, const double *u0, int u0_batched,
+                           const double *mu1, const double *mu2, double At, double E, double tol, int kmax,
+                           double *U, int *iters, void *workspace, void *stream);
+
 /* FEMBurgers.pod_prom_burgers, FEM/fem_burgers.py:709-785 (north_star alias pod_prom_newton), for B
  * samples at once.  Phi: (N, n) row-major (C order) reduced basis shared by all samples.
  * projection: BX_GALERKIN (Ar = Phi^T A Phi, br = Phi^T R, :756-757) or BX_LSPG (J = A Phi,
