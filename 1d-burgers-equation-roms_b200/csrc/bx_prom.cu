@@ -18,7 +18,8 @@
 //         LSPG     Ar = J^T J  (upper block triangle),  br = J^T R        (:760-762)
 //         Galerkin Ar = Phi^T J,                         br = Phi^T R      (:756-757)
 //      R rides along as column n of the B operand, so br is column n of the same accumulators.
-//      q0 = Phi^T U_k (:770) is accumulated in the same pass.
+//      q0 = Phi^T U_k (:770): U_k = Phi q_k for every iterate but the raw u0, so it is (Phi^T Phi) q_k with
+//      Phi^T Phi formed once per CTA; only the first iterate of a trajectory takes an explicit pass.
 //   C  accumulator tiles -> one matrix row per lane (through the dead U_k buffer), n x n LU with
 //      partial pivoting (LAPACK gesv, :767) in registers, pivot rows broadcast through shared
 //      memory, q = q0 + dq, err = |dq| / |q| (:776).
@@ -52,14 +53,16 @@ constexpr int PROM_MAXW = 8;
 // shared-memory carve-up, in doubles.  Node/element arrays are skewed by one word per run so
 // that the four k-lanes of an MMA step (nodes S apart) hit different banks.
 struct PromSmem {
-    int phi, h6, per_cta;                 // CTA-wide: permuted Phi (NP x ldp), h/6 per element
+    int phi, h6, gm, per_cta;             // CTA-wide: permuted Phi (NP x ldp), h/6 per element, Phi^T Phi
     int u, misc, bn, hfs, per_warp, arr;
-    __host__ __device__ static PromSmem make(int NP, int ldp, int phi_smem) {
+    __host__ __device__ static PromSmem make(int NP, int ldp, int phi_smem, int NC) {
         PromSmem m;
         m.arr = NP + 8;
         int o = 0;
         m.phi = o; o += phi_smem ? (NP + 4) * ldp : 0;   // + 4 wrap rows o = (o + 1) & ~1;
         m.h6 = o; o += m.arr;
+        o = (o + 1) & ~1;
+        m.gm = o; o += NC * MAT_LD;
         m.per_cta = (o + 1) & ~1;
         o = 0;
         int usz = m.arr < 16 * MAT_LD - 8 ? 16 * MAT_LD - 8 : m.arr;   // u + first 8 of misc hold the 16 x 33 matrix
@@ -109,9 +112,10 @@ __global__ void __launch_bounds__(PROM_MAXW * 32, 1) prom_kernel(const PromParam
     const int N = p.N, n = p.n, ldp = p.ldp;
     const PromGeom geo = PromGeom::make(N);
     const int S = geo.S, lgS = geo.lgS, NP = geo.NP;
-    const PromSmem lay = PromSmem::make(NP, ldp, PHIS ? 1 : 0);
+    const PromSmem lay = PromSmem::make(NP, ldp, PHIS ? 1 : 0, NC);
     double *s_phi = smem + lay.phi;
     double *s_h6 = smem + lay.h6;
+    double *s_gm = smem + lay.gm;          // Phi^T Phi, NC x MAT_LD
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int t = lane & 3, g = lane >> 2;
@@ -121,7 +125,6 @@ __global__ void __launch_bounds__(PROM_MAXW * 32, 1) prom_kernel(const PromParam
     double *w_bn = wbase + lay.bn;
     double *w_hfs = wbase + lay.hfs;
     double *w_mat = w_u;                 // 16 x MAT_LD, over the dead U_k (+ the first words of misc)
-    double *w_q0 = w_misc + 96;          // q0 = Phi^T U_k        (32)
     double *w_piv = w_misc + 16;         // pivot rows, 2 x (NC+2) (<= 68)
     double *w_q = w_misc + 16;           // q after the solve     (32), over the dead pivot rows
 
@@ -137,6 +140,13 @@ __global__ void __launch_bounds__(PROM_MAXW * 32, 1) prom_kernel(const PromParam
         }
     }
     for (int idx = threadIdx.x; idx < lay.arr; idx += blockDim.x) s_h6[idx] = 0.0;
+    for (int idx = threadIdx.x; idx < NC * NC; idx += blockDim.x) {
+        const int j = idx / NC, m = idx - j * NC;
+        double sum = 0.0;
+        if (j < n && m < n)
+            for (int i = 0; i < N; ++i) sum = fma(p.Phi[(size_t)i * n + j], p.Phi[(size_t)i * n + m], sum);
+        s_gm[j * MAT_LD + m] = sum;
+    }
     __syncthreads();
     for (int e = threadIdx.x; e <= N - 2; e += blockDim.x) s_h6[sk(e, S, lgS)] = (p.X[e + 1] - p.X[e]) / 6.0;
     __syncthreads();
@@ -181,6 +191,19 @@ __global__ void __launch_bounds__(PROM_MAXW * 32, 1) prom_kernel(const PromParam
             }
         }
         __syncwarp();
+        // q0 = Phi^T U_k of the first iterate (the raw u0, which is not in the span of Phi, :716)
+        double q0;
+        {
+            double q4[4] = {0.0, 0.0, 0.0, 0.0};
+            const double *phc = p.Phi + (lane < n ? lane : 0);
+            int i = 0;
+            for (; i + 4 <= N; i += 4) {
+#pragma unroll
+                for (int r = 0; r < 4; ++r) q4[r] = fma(phc[(size_t)(i + r) * n], w_u[sk(i + r, S, lgS)], q4[r]);
+            }
+            for (; i < N; ++i) q4[0] = fma(phc[(size_t)i * n], w_u[sk(i, S, lgS)], q4[0]);
+            q0 = lane < n ? (q4[0] + q4[1]) + (q4[2] + q4[3]) : 0.0;
+        }
 
         for (int step = 0; step < p.nsteps; ++step) {
             // ---- bn = M U^n + At F (:745), constant during the nonlinear loop ------------
@@ -196,9 +219,6 @@ __global__ void __launch_bounds__(PROM_MAXW * 32, 1) prom_kernel(const PromParam
                 double acc[TILES][2];
 #pragma unroll
                 for (int i = 0; i < TILES; ++i) { acc[i][0] = 0.0; acc[i][1] = 0.0; }
-                double pq[NB];
-#pragma unroll
-                for (int b = 0; b < NB; ++b) pq[b] = 0.0;
                 double pm[NB], p0[NB], pp[NB];
                 {
                     const double *rm = PHIS ? s_phi + (((S - 1) << 2) + (t > 0 ? t - 1 : 0)) * ldp
@@ -238,13 +258,9 @@ __global__ void __launch_bounds__(PROM_MAXW * 32, 1) prom_kernel(const PromParam
                         const int src = 4 * j + t;
                         const double ra = shfl_idx(cur.a, src), rb = shfl_idx(cur.b, src);
                         const double rcc = shfl_idx(cur.c, src), rR = shfl_idx(cur.R, src);
-                        const double uk = w_u[ubase + s];
                         double jp[NB];
 #pragma unroll
-                        for (int b = 0; b < NB; ++b) {
-                            jp[b] = fma(ra, pm[b], fma(rb, p0[b], rcc * pp[b]));
-                            pq[b] = fma(p0[b], uk, pq[b]);
-                        }
+                        for (int b = 0; b < NB; ++b) jp[b] = fma(ra, pm[b], fma(rb, p0[b], rcc * pp[b]));
                         if (g == gR) jp[NB - 1] = rR;   // R rides as column n (block NB-1)
 #pragma unroll
                         for (int I = 0; I < NB; ++I) {
@@ -258,17 +274,6 @@ __global__ void __launch_bounds__(PROM_MAXW * 32, 1) prom_kernel(const PromParam
                         for (int b = 0; b < NB; ++b) { pm[b] = p0[b]; p0[b] = pp[b]; }
                     }
                 }
-                // q0 partials: reduce over t (lanes differing in bits 0, 1)
-#pragma unroll
-                for (int b = 0; b < NB; ++b) {
-                    pq[b] += shfl_xor(pq[b], 1);
-                    pq[b] += shfl_xor(pq[b], 2);
-                }
-                if (t == 0) {
-#pragma unroll
-                    for (int b = 0; b < NB; ++b) w_q0[b * 8 + g] = pq[b];
-                }
-
                 // ================= phase C: reduced solve =================================
                 // accumulator tiles -> one matrix row per lane, 16 rows per pass; column n = br
                 double a[NC];
@@ -300,10 +305,9 @@ __global__ void __launch_bounds__(PROM_MAXW * 32, 1) prom_kernel(const PromParam
                         rhs = -mr[n];
                     }
                 }
-                const double q0 = (lane < n) ? w_q0[lane] : 0.0;
                 __syncwarp();
                 const double dq = lu_solve_rows<NC, !LSPG>(a, rhs, n, lane, w_piv);
-                const double q = (lane < n) ? q0 + dq : 0.0;
+                const double q = (lane < n) ? q0 + dq : 0.0;   // q0 = Phi^T U_k (:770)
                 const double sd = warp_sum((lane < n) ? dq * dq : 0.0);
                 const double sq = warp_sum(q * q);
                 const double err = sqrt(sd) / sqrt(sq);
@@ -311,6 +315,15 @@ __global__ void __launch_bounds__(PROM_MAXW * 32, 1) prom_kernel(const PromParam
                 w_q[lane] = q;
                 if (lane == 0) { w_u[sk(-1, S, lgS)] = 0.0; w_u[sk(NP, S, lgS)] = 0.0; }   // halo words the matrix overwrote
                 __syncwarp();
+                // Phi^T U_{k+1} for the next iteration (or time step): U_{k+1} = Phi q, so it is (Phi^T Phi) q
+                {
+                    const double *gr = s_gm + (lane < n ? lane : 0) * MAT_LD;
+                    double s0 = 0.0, s1 = 0.0;
+                    int m = 0;
+                    for (; m + 2 <= n; m += 2) { s0 = fma(gr[m], w_q[m], s0); s1 = fma(gr[m + 1], w_q[m + 1], s1); }
+                    if (m < n) s0 = fma(gr[m], w_q[m], s0);
+                    q0 = (lane < n) ? s0 + s1 : 0.0;
+                }
 
                 // ================= phase D: lift U_{k+1} = Phi q (:773) ===================
                 {
@@ -367,7 +380,7 @@ __global__ void __launch_bounds__(PROM_MAXW * 32, 1) prom_kernel(const PromParam
 template <int NB, bool LSPG, bool PHIS>
 static int launch_prom_t(PromParams p, int min_warps, cudaStream_t st, bool *fits) {
     const PromGeom geo = PromGeom::make(p.N);
-    const PromSmem lay = PromSmem::make(geo.NP, p.ldp, PHIS ? 1 : 0);
+    const PromSmem lay = PromSmem::make(geo.NP, p.ldp, PHIS ? 1 : 0, NB * 8);
     int dev = 0, sms = 0, maxsm = 0;
     BX_CUDA(cudaGetDevice(&dev));
     BX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
