@@ -48,18 +48,23 @@ def test_finemesh_nonuniform_mesh_diffusion_batched_u0(oracle):
 
 
 def test_finemesh_iteration_cap_and_legacy_surface(oracle):
-    """dt = 0.05 on a 4097-node mesh does not converge (SURVEY: diverges for N >= 768): the first step stops at
-    the 20-iteration cap exactly as the reference's while-loop does.  (Later steps of this diverging run grow to
-    1e12 and beyond, where parity is meaningless -- SURVEY 8d, config 5b.)"""
+    """dt = 0.05 on a 4097-node mesh does not converge (SURVEY: diverges for N >= 768): the step stops at the
+    iteration cap exactly as the reference's while-loop does.  The diverging Picard map is chaotic: a 1e-15
+    relative perturbation of u0 changes the ORACLE's own 20th iterate by O(1) (1e-12 after 5 iterations, 1e-7 after
+    10, 8e-2 after 15 -- measured with oracle.fom_burgers), so values are compared at a cap of 5, where rounding
+    differences are still below the 1e-10 bar, and the reference's cap of 20 is checked for the count only
+    (no parity claim there)."""
     import burgers_b200
     N = 4097
     X = np.linspace(0.0, 100.0, N)
     fem = burgers_b200.FEMBurgers(X)
+    U, it = fem.fom_burgers_batch(0.05, 1, np.ones(N), [4.75], 0.0, [0.02], kmax=5)
+    Uo, ito = oracle.fom_burgers(X, 0.05, 1, np.ones(N), 4.75, 0.0, 0.02, kmax=5)
+    assert np.array_equal(it[0].cpu().numpy(), ito) and np.all(ito == 5)
+    assert rel_l2_per_step(U[0].cpu().numpy().T, Uo) <= TOL
     U = fem.fom_burgers(0.05, 1, np.ones(N), 4.75, 0.0, 0.02)
-    Uo, ito = oracle.fom_burgers(X, 0.05, 1, np.ones(N), 4.75, 0.0, 0.02)
     assert U.shape == (N, 2) and U.dtype == np.float64
-    assert np.array_equal(fem.last_iters, ito) and np.all(ito == 20)
-    assert rel_l2_per_step(U, Uo) <= 1e-8    # unconverged, growing iterates: rounding differences are amplified
+    assert np.all(fem.last_iters == 20) and np.all(np.isfinite(U)) and U[0, 1] == 4.75
 
 
 def test_finemesh_full_size_properties(oracle):
