@@ -102,6 +102,19 @@ __global__ void __launch_bounds__(256) prom_forcing_kernel(int B, int N, const d
 }
 
 
+int launch_prom_forcing(int B, int N, const double *X, const double *mu2, double At, double *atf, double *hfs,
+                        cudaStream_t st) {
+    prom_forcing_kernel<<<(unsigned)(((long long)B * N + 255) / 256), 256, 0, st>>>(B, N, X, mu2, At, atf, hfs);
+    BX_LAUNCH_CHECK();
+    return BX_OK;
+}
+
+// bx_prom_cta.cu: one CTA per trajectory, 32 <= n <= 240
+int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const double *u0, int u0_batched,
+                    const double *mu1, const double *mu2, double At, double E, const double *Phi, int projection,
+                    double tol, int kmax, double *U, int *iters, void *workspace, long long mat_offset_bytes,
+                    cudaStream_t st, long long *mat_bytes_out);
+
 template <int NB, bool LSPG, bool PHIS>
 __global__ void __launch_bounds__(PROM_MAXW * 32, 1) prom_kernel(const PromParams p) {
     constexpr int NC = NB * 8;
@@ -425,15 +438,25 @@ static int launch_prom(const PromParams &p, cudaStream_t st) {
     if (p.n <= 15) return launch_prom_nb<2, LSPG>(p, st);
     if (p.n <= 23) return launch_prom_nb<3, LSPG>(p, st);
     if (p.n <= 31) return launch_prom_nb<4, LSPG>(p, st);
-    set_error("bx_prom_trajectories: n = %d modes > 31 is not supported by this kernel", p.n);
+    set_error("bx_prom_trajectories: internal dispatch error (n = %d)", p.n);
     return BX_ERR_UNSUPPORTED;
 }
 
 }  // namespace bx
 
-extern "C" long long bx_prom_workspace_bytes(int B, int N) {
-    if (B < 0 || N < 0) return -1;
-    return 256 + 2LL * (long long)B * (long long)N * (long long)sizeof(double);
+static long long prom_forcing_bytes(int B, int N) {
+    return (256 + 2LL * (long long)B * (long long)N * (long long)sizeof(double) + 15) & ~15LL;
+}
+
+extern "C" long long bx_prom_workspace_bytes(int B, int N, int n) {
+    if (B < 0 || N < 2 || n < 1) return -1;
+    long long mat = 0;
+    if (n >= 32 && n <= 240) {
+        if (bx::launch_prom_cta(B, N, n, 0, nullptr, nullptr, 0, nullptr, nullptr, 0.0, 0.0, nullptr, BX_GALERKIN, 0.0, 1,
+                                nullptr, nullptr, nullptr, 0, nullptr, &mat) != BX_OK)
+            return -1;
+    }
+    return prom_forcing_bytes(B, N) + mat;
 }
 
 extern "C" int bx_prom_trajectories(int B, int N, int n, int nsteps, const double *X, const double *u0,
@@ -451,6 +474,14 @@ extern "C" int bx_prom_trajectories(int B, int N, int n, int nsteps, const doubl
     BX_REQUIRE(kmax >= 1, "kmax must be >= 1 (the reference loop body defines U1)");
     if (B == 0) return BX_OK;
     BX_REQUIRE(X && u0 && mu1 && mu2 && Phi && U && workspace, "null device pointer");
+    if (n >= 32) {
+        if (n > 240) {
+            set_error("bx_prom_trajectories: n = %d modes > 240 is not supported by this build", n);
+            return BX_ERR_UNSUPPORTED;
+        }
+        return launch_prom_cta(B, N, n, nsteps, X, u0, u0_batched, mu1, mu2, At, E, Phi, projection, tol, kmax, U,
+                               iters, workspace, prom_forcing_bytes(B, N), static_cast<cudaStream_t>(stream), nullptr);
+    }
     PromParams p;
     p.B = B; p.N = N; p.n = n; p.nsteps = nsteps; p.kmax = kmax;
     p.ldp = ((n + 3) / 8) * 8 + 4;   // smallest stride >= n that is 4 mod 8: conflict-free fragment loads

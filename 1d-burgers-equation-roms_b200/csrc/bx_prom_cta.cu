@@ -1,0 +1,558 @@
+// bx_prom_cta.cu — POD-PROM trajectory kernel for LARGE bases (32 <= n <= 240 modes):
+// FEMBurgers.pod_prom_burgers (FEM/fem_burgers.py:709-785), Galerkin and LSPG.  The reference's own driver
+// runs 40 modes (POD/Results_thesis/prom_pod.py:35, tol 1e-3) and its stored truncations go up to 227.
+//
+// One CTA (4, 8 or 16 warps) integrates one trajectory; CTAs pull samples from an atomic queue.  The basis
+// Phi (N x n, up to 0.9 MB) no longer fits next to the work tiles, so it streams from L2 in chunks of KC nodes
+// (cp.async, three-deep ring); the state, the bands and the n x n reduced system stay in shared memory for the
+// whole trajectory (the reduced system moves to an L2-resident scratch when it exceeds what is left, n >~ 140).
+//
+// One nonlinear iteration (:726-781):
+//   A  rows of A = M + At C(U_k) + At E K (row 0 <- e0^T) and of R = A U_k - b, one node per thread (prom_row).
+//   B  per chunk: J = A Phi from the three bands (3 DFMA per entry, R as column n), q0 += Phi^T U_k partials,
+//      then the contraction on the FP64 tensor pipe (mma.sync.m8n8k4.f64), k index = node, 16 x 16 output
+//      units (2 x 2 DMMA tiles) dealt round-robin to the warps, at most UB units per warp per pass over the
+//      nodes:  LSPG  Ar = J^T J (upper unit triangle, mirrored), br = J^T R;  Galerkin  Ar = Phi^T J, br = Phi^T R.
+//      Staging of chunk c+2, J of chunk c+1 and the DMMAs of chunk c share one barrier interval.
+//   C  blocked right-looking LU of [Ar | br], panel width 8, one matrix row per thread in the panel (partial
+//      pivoting in gesv's elimination order for Galerkin, :767; natural order for the SPD LSPG normal matrix;
+//      rows never move — implicit pivoting), rank-8 trailing update with the U12 column in registers and the
+//      L21 rows broadcast from a packed shared-memory panel; blocked back substitution.
+//   D  q = q0 + dq, err = |dq| / |q| (:776), lift U_{k+1} = Phi q (:773), one warp per node.
+// HBM traffic: the 8N-byte snapshot per time step; Phi is re-read from L2 twice per iteration.
+#include "bx_prom_common.cuh"
+#include "bx_async.cuh"
+
+namespace bx {
+
+// defined in bx_prom.cu: per-sample forcing data At F and (h/6)(f1 + f2) into the workspace
+int launch_prom_forcing(int B, int N, const double *X, const double *mu2, double At, double *atf, double *hfs,
+                        cudaStream_t st);
+
+constexpr int PC_UB = 4;        // 16 x 16 output units a warp accumulates per pass (32 FP64 accumulators)
+constexpr int PC_MAXW = 16;
+constexpr int PC_NMAX = 240;    // NC = 16 ceil((n+1)/16) <= 256 = 8 columns per lane in the J pass
+
+struct PromCtaParams {
+    int B, N, n, nsteps, kmax;
+    int NBu, NC, ldp, ldm, KC, nchunks, NPad, units, passes, lgS;
+    int mat_global;
+    const double *X;
+    const double *u0;
+    long long u0_stride;
+    const double *mu1;
+    const double *mu2;
+    double At, E, tol;
+    const double *Phi;
+    double *atf, *hfs;
+    double *mat_ws;      // per-CTA reduced system when it does not fit in shared memory
+    double *U;
+    int *iters;
+    unsigned int *counter;
+};
+
+// shared-memory carve-up (doubles), identical on host and device
+struct PromCtaSmem {
+    int h6, u, bn, hfs, ra, rb, rc, rR, q, q0, x, prow, cand, red2, ints, work, phi, J, L, red, mat, total;
+    int arr, phisz, Jsz;
+    __host__ __device__ static PromCtaSmem make(int N, int n, int NC, int ldp, int ldm, int KC, int NPad, int lgS,
+                                                int W, int mat_in_smem) {
+        PromCtaSmem m;
+        const int S = 1 << lgS;
+        m.arr = S + 4;
+        int o = 0;
+        m.h6 = o; o += m.arr;
+        m.u = o; o += m.arr;
+        m.bn = o; o += m.arr;
+        m.hfs = o; o += m.arr;
+        m.ra = o; o += NPad;
+        m.rb = o; o += NPad;
+        m.rc = o; o += NPad;
+        m.rR = o; o += NPad;
+        m.q = o; o += NC;
+        m.q0 = o; o += NC;
+        m.x = o; o += NC;
+        m.prow = o; o += 16;
+        m.cand = o; o += 4 * PC_MAXW;       // 2 buffers x W x (key, index)
+        m.red2 = o; o += 2 * PC_MAXW + 2;
+        m.ints = o; o += NC + NC / 4 + 8;   // pivrow[NC] (int), act[NC] (int) -> NC doubles; cnt[W] + misc
+        o = (o + 1) & ~1;
+        m.work = o;
+        // work region: chunk ring during the contraction, packed L21 panel / reductions afterwards
+        m.phisz = (KC + 2) * ldp;
+        m.Jsz = KC * ldp;
+        m.phi = o; m.J = o + 3 * m.phisz;
+        int wsz = 3 * m.phisz + 2 * m.Jsz;
+        m.L = o;                             // NC x 8, 16-byte aligned rows
+        m.red = o;                           // W x NC partial q0
+        if (wsz < NC * 8) wsz = NC * 8;
+        if (wsz < W * NC) wsz = W * NC;
+        o += wsz;
+        o = (o + 1) & ~1;
+        m.mat = o;
+        if (mat_in_smem) o += n * ldm;
+        m.total = o;
+        return m;
+    }
+};
+
+__device__ __forceinline__ void cp_async8(double *dst, const double *src, bool ok) {
+    const unsigned sz = ok ? 8u : 0u;
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+template <bool LSPG>
+__global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCtaParams p) {
+    extern __shared__ __align__(16) double smem[];
+    const int N = p.N, n = p.n, NC = p.NC, ldp = p.ldp, ldm = p.ldm, KC = p.KC, lgS = p.lgS;
+    const int S = 1 << lgS;
+    const int T = blockDim.x, W = T >> 5;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int t = lane & 3, g = lane >> 2;
+    const PromCtaSmem lay = PromCtaSmem::make(N, n, NC, ldp, ldm, KC, p.NPad, lgS, W, p.mat_global ? 0 : 1);
+    double *s_h6 = smem + lay.h6, *s_u = smem + lay.u, *s_bn = smem + lay.bn, *s_hfs = smem + lay.hfs;
+    double *s_ra = smem + lay.ra, *s_rb = smem + lay.rb, *s_rc = smem + lay.rc, *s_rR = smem + lay.rR;
+    double *s_q = smem + lay.q, *s_q0 = smem + lay.q0, *s_x = smem + lay.x, *s_prow = smem + lay.prow;
+    double *s_cand = smem + lay.cand, *s_red2 = smem + lay.red2;
+    int *s_pivrow = reinterpret_cast<int *>(smem + lay.ints);
+    int *s_act = s_pivrow + NC;
+    int *s_cnt = s_act + NC;            // W warp counts, then [W] = next sample
+    double *s_phi = smem + lay.phi, *s_J = smem + lay.J, *s_L = smem + lay.L, *s_red = smem + lay.red;
+    double *mat = p.mat_global ? p.mat_ws + (size_t)blockIdx.x * (size_t)n * ldm : smem + lay.mat;
+
+    // ---- CTA prologue: mesh constants, halo words ---------------------------------------------
+    for (int i = tid; i < lay.arr; i += T) { s_h6[i] = 0.0; s_u[i] = 0.0; s_bn[i] = 0.0; s_hfs[i] = 0.0; }
+    __syncthreads();
+    for (int e = tid; e <= N - 2; e += T) s_h6[sk(e, S, lgS)] = (p.X[e + 1] - p.X[e]) / 6.0;
+
+    PromRowCtx rc;
+    rc.u = s_u; rc.bn = s_bn; rc.hfs = s_hfs; rc.h6 = s_h6;
+    rc.a6 = p.At / 6.0; rc.c1 = 1.5 * p.At; rc.ate = p.At * p.E; rc.has_e = p.E != 0.0; rc.supg = true;
+    rc.N = N; rc.S = S; rc.lgS = lgS;
+
+    const int mcols = (NC + 31) >> 5;   // columns per lane in the J pass (<= 8)
+
+    for (;;) {
+        __syncthreads();
+        if (tid == 0) s_cnt[W] = (int)atomicAdd(p.counter, 1u);
+        __syncthreads();
+        const int smp = s_cnt[W];
+        if (smp >= p.B) break;
+        rc.mu1 = p.mu1[smp];
+        const double *atf = p.atf + (size_t)smp * N;
+        double *Us = p.U + (long long)smp * (long long)(p.nsteps + 1) * N;
+        {
+            const double *hf = p.hfs + (size_t)smp * N;
+            const double *u0p = p.u0 + (long long)smp * p.u0_stride;
+            for (int i = tid; i < N; i += T) {
+                const int o = sk(i, S, lgS);
+                s_hfs[o] = i <= N - 2 ? hf[i] : 0.0;
+                const double v = u0p[i];
+                s_u[o] = v;
+                Us[i] = v;
+            }
+        }
+        __syncthreads();
+
+        for (int step = 0; step < p.nsteps; ++step) {
+            // ---- bn = M U^n + At F (:745) ------------------------------------------------------
+            for (int i = tid; i < N; i += T) {
+                const double h6L = s_h6[sk(i - 1, S, lgS)], h6R = s_h6[sk(i, S, lgS)];
+                const double um = s_u[sk(i - 1, S, lgS)], uc = s_u[sk(i, S, lgS)], up = s_u[sk(i + 1, S, lgS)];
+                s_bn[sk(i, S, lgS)] = h6L * um + (2.0 * (h6L + h6R)) * uc + h6R * up + atf[i];
+            }
+            __syncthreads();
+            int k = 0;
+            for (;;) {
+                // ================= phase A: rows of A and R (:730-752) =========================
+                for (int i = tid; i < p.NPad; i += T) {
+                    PromRow r;
+                    if (i < N) r = prom_row(rc, i, sk(i, S, lgS));
+                    else { r.a = 0.0; r.b = 0.0; r.c = 0.0; r.R = 0.0; }
+                    s_ra[i] = r.a; s_rb[i] = r.b; s_rc[i] = r.c; s_rR[i] = r.R;
+                }
+                // (the barrier after the first staging below orders these writes before their readers)
+
+                // ================= phase B: J = A Phi, contraction (:756-762) ====================
+                double q0acc[8];
+#pragma unroll
+                for (int m = 0; m < 8; ++m) q0acc[m] = 0.0;
+
+                auto stage_phi = [&](int c) {
+                    double *dst = s_phi + (c % 3) * lay.phisz;
+                    for (int r = warp; r < KC + 2; r += W) {
+                        const int i = c * KC - 1 + r;
+                        const bool rok = i >= 0 && i < N;
+                        const double *src = p.Phi + (size_t)(rok ? i : 0) * n;
+                        for (int j = lane; j < NC; j += 32) cp_async8(dst + r * ldp + j, src + (j < n ? j : 0), rok && j < n);
+                    }
+                };
+                auto compute_J = [&](int c, bool with_q0) {
+                    const double *ph = s_phi + (c % 3) * lay.phisz;
+                    double *Jc = s_J + (c & 1) * lay.Jsz;
+                    for (int kk = warp; kk < KC; kk += W) {
+                        const int i = c * KC + kk;
+                        const double ra = s_ra[i], rb = s_rb[i], rcc = s_rc[i], rR = s_rR[i];
+                        const double ui = (with_q0 && i < N) ? s_u[sk(i, S, lgS)] : 0.0;
+                        const double *r0 = ph + kk * ldp;
+#pragma unroll
+                        for (int m = 0; m < 8; ++m) {
+                            const int j = lane + 32 * m;
+                            if (m < mcols && j < NC) {
+                                const double pm = r0[j], p0 = r0[ldp + j], pp = r0[2 * ldp + j];
+                                double v = fma(ra, pm, fma(rb, p0, rcc * pp));
+                                if (j == n) v = rR;
+                                Jc[kk * ldp + j] = v;
+                                q0acc[m] = fma(p0, ui, q0acc[m]);
+                            }
+                        }
+                    }
+                };
+
+                for (int pass = 0; pass < p.passes; ++pass) {
+                    double acc[PC_UB][4][2];
+                    int offA[PC_UB], offB[PC_UB];
+                    bool uval[PC_UB], udiag[PC_UB];
+#pragma unroll
+                    for (int s = 0; s < PC_UB; ++s) {
+#pragma unroll
+                        for (int q4 = 0; q4 < 4; ++q4) { acc[s][q4][0] = 0.0; acc[s][q4][1] = 0.0; }
+                        const int u = (pass * PC_UB + s) * W + warp;
+                        uval[s] = u < p.units;
+                        int Iu = 0, Ju = 0;
+                        if (uval[s]) {
+                            if (LSPG) {
+                                int rem = u;
+                                while (rem >= p.NBu - Iu) { rem -= p.NBu - Iu; ++Iu; }
+                                Ju = Iu + rem;
+                            } else {
+                                Iu = u / p.NBu; Ju = u - Iu * p.NBu;
+                            }
+                        }
+                        udiag[s] = Iu == Ju;
+                        offA[s] = Iu * 16 + g; offB[s] = Ju * 16 + g;
+                    }
+                    stage_phi(0);
+                    if (p.nchunks > 1) stage_phi(1);
+                    cp_async_wait_all();
+                    __syncthreads();
+                    compute_J(0, pass == 0);
+                    __syncthreads();
+                    for (int c = 0; c < p.nchunks; ++c) {
+                        if (c + 2 < p.nchunks) stage_phi(c + 2);
+                        if (c + 1 < p.nchunks) compute_J(c + 1, pass == 0);
+                        const double *Jc = s_J + (c & 1) * lay.Jsz;
+                        const double *Ac = LSPG ? Jc : s_phi + (c % 3) * lay.phisz + ldp;
+                        for (int ks = 0; ks < KC; ks += 4) {
+                            const int ro = (ks + t) * ldp;
+#pragma unroll
+                            for (int s = 0; s < PC_UB; ++s) {
+                                if (uval[s]) {
+                                    const double a0 = Ac[ro + offA[s]], a1 = Ac[ro + offA[s] + 8];
+                                    const double b0 = Jc[ro + offB[s]], b1 = Jc[ro + offB[s] + 8];
+                                    dmma884(acc[s][0][0], acc[s][0][1], a0, b0);
+                                    dmma884(acc[s][1][0], acc[s][1][1], a0, b1);
+                                    dmma884(acc[s][2][0], acc[s][2][1], a1, b0);
+                                    dmma884(acc[s][3][0], acc[s][3][1], a1, b1);
+                                }
+                            }
+                        }
+                        cp_async_wait_all();
+                        __syncthreads();
+                    }
+                    // accumulator tiles -> [Ar | br]; column n = br
+#pragma unroll
+                    for (int s = 0; s < PC_UB; ++s) {
+                        if (uval[s]) {
+#pragma unroll
+                            for (int q4 = 0; q4 < 4; ++q4) {
+                                const int r = (offA[s] - g) + (q4 >> 1) * 8 + g;
+                                const int c0 = (offB[s] - g) + (q4 & 1) * 8 + 2 * t;
+#pragma unroll
+                                for (int e = 0; e < 2; ++e) {
+                                    const int c = c0 + e;
+                                    const double v = acc[s][q4][e];
+                                    if (r < n && c <= n) mat[r * ldm + c] = v;
+                                    if (LSPG && !udiag[s] && c < n && r < n) mat[c * ldm + r] = v;
+                                }
+                            }
+                        }
+                    }
+                }
+                // q0 = Phi^T U_k (:770): per-warp partials summed in warp order
+#pragma unroll
+                for (int m = 0; m < 8; ++m) {
+                    const int j = lane + 32 * m;
+                    if (m < mcols && j < NC) s_red[warp * NC + j] = q0acc[m];
+                }
+                __syncthreads();
+                if (tid < NC) {
+                    double sum = 0.0;
+                    for (int w = 0; w < W; ++w) sum += s_red[w * NC + tid];
+                    s_q0[tid] = tid < n ? sum : 0.0;
+                }
+                __syncthreads();
+
+                // ================= phase C: blocked LU of [Ar | br], one row per thread ==========
+                bool done = tid >= n;
+                for (int k0 = 0; k0 < n; k0 += 8) {
+                    const int w = n - k0 < 8 ? n - k0 : 8;
+                    const bool doneprev = done;
+                    double pv[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) pv[j] = (!done && j < w) ? mat[tid * ldm + k0 + j] : 0.0;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        if (j < w) {
+                            int win = k0 + j;
+                            if (!LSPG) {   // idamax of dgetf2 over the rows not yet used as pivots
+                                const unsigned long long key =
+                                    done ? 0ull : (unsigned long long)__double_as_longlong(fabs(pv[j])) + 1ull;
+                                const unsigned khi = (unsigned)(key >> 32), klo = (unsigned)key;
+                                const unsigned mhi = __reduce_max_sync(FULL, khi);
+                                const bool c1 = khi == mhi;
+                                const unsigned mlo = __reduce_max_sync(FULL, c1 ? klo : 0u);
+                                const unsigned ball = __ballot_sync(FULL, c1 && klo == mlo && !done);
+                                if (lane == 0) {
+                                    double *cd = s_cand + (j & 1) * 2 * PC_MAXW + 2 * warp;
+                                    cd[0] = __longlong_as_double(ball ? (long long)(((unsigned long long)mhi << 32) | mlo) : 0ll);
+                                    cd[1] = (double)(ball ? (warp << 5) + (__ffs(ball) - 1) : -1);
+                                }
+                                __syncthreads();
+                                unsigned long long best = 0ull;
+                                win = -1;
+                                for (int ww = 0; ww < W; ++ww) {
+                                    const double *cd = s_cand + (j & 1) * 2 * PC_MAXW + 2 * ww;
+                                    const unsigned long long kk = (unsigned long long)__double_as_longlong(cd[0]);
+                                    if (kk > best) { best = kk; win = (int)cd[1]; }
+                                }
+                                if (win < 0) win = k0 + j;   // only non-finite systems get here
+                            }
+                            if (tid == win) {
+#pragma unroll
+                                for (int jj = 0; jj < 8; ++jj) s_prow[(j & 1) * 8 + jj] = pv[jj];
+                                done = true;
+                                s_pivrow[k0 + j] = tid;
+                            }
+                            __syncthreads();
+                            if (!done) {
+                                const double *pr = s_prow + (j & 1) * 8;
+                                const double l = pv[j] * rcp(pr[j]);
+                                pv[j] = l;
+#pragma unroll
+                                for (int jj = j + 1; jj < 8; ++jj) pv[jj] = fma(-l, pr[jj], pv[jj]);
+                            }
+                        }
+                    }
+                    // pivot rows of this block back to the matrix (L11 / U11); multipliers to the packed panel
+                    if (done && !doneprev) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) if (j < w) mat[tid * ldm + k0 + j] = pv[j];
+                    }
+                    int pos = -1;
+                    if (LSPG) {
+                        if (!done) pos = tid - (k0 + w);
+                    } else {
+                        const unsigned act = __ballot_sync(FULL, !done);
+                        if (lane == 0) s_cnt[warp] = __popc(act);
+                        __syncthreads();
+                        if (!done) {
+                            pos = __popc(act & ((1u << lane) - 1u));
+                            for (int ww = 0; ww < warp; ++ww) pos += s_cnt[ww];
+                        }
+                    }
+                    if (pos >= 0) {
+                        double2 *Lr = reinterpret_cast<double2 *>(s_L + pos * 8);
+                        Lr[0] = make_double2(pv[0], pv[1]); Lr[1] = make_double2(pv[2], pv[3]);
+                        Lr[2] = make_double2(pv[4], pv[5]); Lr[3] = make_double2(pv[6], pv[7]);
+                        s_act[pos] = tid;
+                    }
+                    __syncthreads();
+                    const int nact = n - (k0 + w);
+                    // U12 column in registers, then the rank-w update of the rows still in play
+                    const int ncols = n - (k0 + w) + 1;
+                    const int CW = (ncols + 31) & ~31;
+                    const int RG = T / CW;
+                    const int cidx = tid % CW, rg = tid / CW;
+                    const bool cok = cidx < ncols && rg < RG;
+                    const int col = k0 + w + cidx;
+                    double uu[8];
+                    int prw[8];
+                    if (cok) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            uu[j] = 0.0; prw[j] = 0;
+                            if (j < w) {
+                                prw[j] = s_pivrow[k0 + j];
+                                double v = mat[prw[j] * ldm + col];
+#pragma unroll
+                                for (int jj = 0; jj < j; ++jj) v = fma(-mat[prw[j] * ldm + k0 + jj], uu[jj], v);
+                                uu[j] = v;
+                            }
+                        }
+                        for (int ps = rg; ps < nact; ps += RG) {
+                            const double2 *Lr = reinterpret_cast<const double2 *>(s_L + ps * 8);
+                            const double2 l01 = Lr[0], l23 = Lr[1], l45 = Lr[2], l67 = Lr[3];
+                            double *ap = mat + s_act[ps] * ldm + col;
+                            double v = *ap;
+                            v = fma(-l01.x, uu[0], v); v = fma(-l01.y, uu[1], v);
+                            v = fma(-l23.x, uu[2], v); v = fma(-l23.y, uu[3], v);
+                            v = fma(-l45.x, uu[4], v); v = fma(-l45.y, uu[5], v);
+                            v = fma(-l67.x, uu[6], v); v = fma(-l67.y, uu[7], v);
+                            *ap = v;
+                        }
+                    }
+                    __syncthreads();
+                    if (cok && rg == 0) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) if (j < w) mat[prw[j] * ldm + col] = uu[j];
+                    }
+                }
+                __syncthreads();
+                // ---- blocked back substitution: U x = y, thread k owns unknown k -----------------
+                {
+                    int pr = 0;
+                    double y = 0.0;
+                    if (tid < n) { pr = s_pivrow[tid]; y = mat[pr * ldm + n]; }
+                    for (int k0 = ((n - 1) >> 3) << 3; k0 >= 0; k0 -= 8) {
+                        const int w = n - k0 < 8 ? n - k0 : 8;
+                        if (warp == (k0 >> 5)) {
+                            const int l0 = k0 & 31;
+                            const double dinv = (tid < n) ? rcp(mat[pr * ldm + tid]) : 0.0;
+                            for (int j = w - 1; j >= 0; --j) {
+                                const double xj = shfl_idx(y * dinv, l0 + j);
+                                if (lane >= l0 && lane < l0 + j) y = fma(-mat[pr * ldm + k0 + j], xj, y);
+                                if (lane == l0 + j) s_x[k0 + j] = xj;
+                            }
+                        }
+                        __syncthreads();
+                        if (tid < k0) {
+#pragma unroll
+                            for (int j = 0; j < 8; ++j)
+                                if (j < w) y = fma(-mat[pr * ldm + k0 + j], s_x[k0 + j], y);
+                        }
+                    }
+                }
+                // ================= phase D: q = q0 + dq, error, lift (:770-776) ====================
+                double err;
+                {
+                    double dq = 0.0, q = 0.0;
+                    if (tid < n) { dq = -s_x[tid]; q = s_q0[tid] + dq; }
+                    if (tid < NC) s_q[tid] = q;
+                    const double sd = warp_sum(dq * dq), sq = warp_sum(q * q);
+                    if (lane == 0) { s_red2[2 * warp] = sd; s_red2[2 * warp + 1] = sq; }
+                    __syncthreads();
+                    double a = 0.0, b = 0.0;
+                    for (int ww = 0; ww < W; ++ww) { a += s_red2[2 * ww]; b += s_red2[2 * ww + 1]; }
+                    err = sqrt(a) / sqrt(b);
+                }
+                for (int i0 = warp * 4; i0 < N; i0 += W * 4) {
+                    double v[4] = {0.0, 0.0, 0.0, 0.0};
+                    for (int j = lane; j < n; j += 32) {
+                        const double qj = s_q[j];
+#pragma unroll
+                        for (int r = 0; r < 4; ++r)
+                            if (i0 + r < N) v[r] = fma(p.Phi[(size_t)(i0 + r) * n + j], qj, v[r]);
+                    }
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) {
+                        const double sum = warp_sum(v[r]);
+                        if (lane == 0 && i0 + r < N) s_u[sk(i0 + r, S, lgS)] = sum;
+                    }
+                }
+                __syncthreads();
+                ++k;
+                if (!(err > p.tol) || k >= p.kmax) break;
+            }
+            // ---- snapshot step+1 (:783) and iteration count ------------------------------------
+            double *Un1 = Us + (long long)(step + 1) * N;
+            for (int i = tid; i < N; i += T) Un1[i] = s_u[sk(i, S, lgS)];
+            if (tid == 0 && p.iters) p.iters[(long long)smp * p.nsteps + step] = k;
+        }
+    }
+}
+
+// ---- host: geometry, shared-memory fit, launch ----------------------------------------------------
+int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const double *u0, int u0_batched,
+                    const double *mu1, const double *mu2, double At, double E, const double *Phi, int projection,
+                    double tol, int kmax, double *U, int *iters, void *workspace, long long mat_offset_bytes,
+                    cudaStream_t st, long long *mat_bytes_out) {
+    PromCtaParams p;
+    p.B = B; p.N = N; p.n = n; p.nsteps = nsteps; p.kmax = kmax;
+    p.NBu = (n + 1 + 15) / 16;
+    p.NC = 16 * p.NBu;
+    p.ldp = p.NC + 4;                 // 4 mod 8: conflict-free DMMA fragment loads
+    p.ldm = (n + 1) | 1;              // odd, >= n + 1
+    p.units = projection == BX_LSPG ? p.NBu * (p.NBu + 1) / 2 : p.NBu * p.NBu;
+    int W = 4;
+    while (W < PC_MAXW && (W * PC_UB < p.units || W * 32 < p.NC)) W *= 2;
+    p.passes = (p.units + W * PC_UB - 1) / (W * PC_UB);
+    p.lgS = 3;
+    while ((1 << p.lgS) < N) ++p.lgS;
+    int dev = 0, sms = 0, maxsm = 0;
+    BX_CUDA(cudaGetDevice(&dev));
+    BX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    BX_CUDA(cudaDeviceGetAttribute(&maxsm, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+    // largest chunk that fits, reduced system in shared memory if possible
+    static const int kcs[3] = {32, 16, 8};
+    PromCtaSmem lay;
+    bool found = false;
+    for (int mg = 0; mg < 2 && !found; ++mg) {
+        for (int ki = 0; ki < 3 && !found; ++ki) {
+            if (mg == 0 && kcs[ki] == 32 && n > 64) continue;   // leave room for a second CTA per SM
+            p.KC = kcs[ki];
+            p.nchunks = (N + p.KC - 1) / p.KC;
+            p.NPad = p.nchunks * p.KC;
+            p.mat_global = mg;
+            lay = PromCtaSmem::make(N, n, p.NC, p.ldp, p.ldm, p.KC, p.NPad, p.lgS, W, mg ? 0 : 1);
+            found = (long long)lay.total * (long long)sizeof(double) <= (long long)maxsm;
+        }
+    }
+    // resident CTAs per SM can never exceed what shared memory allows (1 KB reserved per CTA)
+    int occ_bound = found ? (int)(233472LL / ((long long)lay.total * (long long)sizeof(double) + 1024)) : 1;
+    if (occ_bound < 1) occ_bound = 1;
+    if (occ_bound > 4) occ_bound = 4;
+    if (mat_bytes_out) {   // workspace query: one reduced system per resident CTA when it lives in global memory
+        *mat_bytes_out = (found && p.mat_global) ? (long long)sms * occ_bound * (long long)n * p.ldm * (long long)sizeof(double) : 0;
+        return BX_OK;
+    }
+    if (!found) {
+        set_error("bx_prom_trajectories: N = %d, n = %d does not fit in shared memory", N, n);
+        return BX_ERR_UNSUPPORTED;
+    }
+    p.X = X; p.u0 = u0; p.u0_stride = u0_batched ? N : 0;
+    p.mu1 = mu1; p.mu2 = mu2; p.At = At; p.E = E; p.tol = tol;
+    p.Phi = Phi; p.U = U; p.iters = iters;
+    p.counter = static_cast<unsigned int *>(workspace);
+    p.atf = reinterpret_cast<double *>(static_cast<char *>(workspace) + 256);
+    p.hfs = p.atf + (size_t)B * N;
+    p.mat_ws = reinterpret_cast<double *>(static_cast<char *>(workspace) + mat_offset_bytes);
+    const size_t smem = sizeof(double) * (size_t)lay.total;
+    int occ = 0;
+    if (projection == BX_LSPG) {
+        BX_CUDA(cudaFuncSetAttribute(prom_cta_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        BX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, prom_cta_kernel<true>, W * 32, smem));
+    } else {
+        BX_CUDA(cudaFuncSetAttribute(prom_cta_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        BX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, prom_cta_kernel<false>, W * 32, smem));
+    }
+    if (occ < 1) {
+        set_error("bx_prom_trajectories: kernel does not fit on an SM (N = %d, n = %d)", N, n);
+        return BX_ERR_UNSUPPORTED;
+    }
+    if (occ > occ_bound) occ = occ_bound;
+    long long ctas = (long long)sms * occ;
+    if (ctas > B) ctas = B;
+    BX_CUDA(cudaMemsetAsync(p.counter, 0, sizeof(unsigned int), st));
+    {
+        const int rcf = launch_prom_forcing(B, N, X, mu2, At, p.atf, p.hfs, st);
+        if (rcf != BX_OK) return rcf;
+    }
+    if (projection == BX_LSPG) prom_cta_kernel<true><<<(unsigned)ctas, W * 32, smem, st>>>(p);
+    else prom_cta_kernel<false><<<(unsigned)ctas, W * 32, smem, st>>>(p);
+    BX_LAUNCH_CHECK();
+    return BX_OK;
+}
+
+}  // namespace bx

@@ -284,10 +284,12 @@ class FEMBurgers:
         if B == 0:
             return U, iters
         lib = _lib.load()
+        need = int(lib.bx_prom_workspace_bytes(B, N, n))
+        if need < 0:
+            raise _lib.BurgersB200Error("bx_prom_workspace_bytes failed: " + lib.bx_last_error().decode())
         _lib.check(lib.bx_prom_trajectories(B, N, n, nT, _ptr(self.Xd), _ptr(u0), batched, _ptr(mu1), _ptr(mu2),
                                             float(At), float(E), _ptr(Phi), code, float(tol), int(kmax),
-                                            _ptr(U), _ptr(iters),
-                                            _ptr(self._scratch(int(lib.bx_prom_workspace_bytes(B, N)))), _stream()),
+                                            _ptr(U), _ptr(iters), _ptr(self._scratch(need)), _stream()),
                    "bx_prom_trajectories")
         return U, iters
 

@@ -105,10 +105,12 @@ int bx_fom_picard_finemesh(int B, int N, int nsteps, const double *X, const doub
  * projection: BX_GALERKIN (Ar = Phi^T A Phi, br = Phi^T R, :756-757) or BX_LSPG (J = A Phi,
  * Ar = J^T J, br = J^T R, :760-762); anything else returns BX_ERR_PROJECTION (ValueError, :764).
  * The reduced solve is LU with partial pivoting (np.linalg.solve -> LAPACK gesv, :767).
- * tol, kmax: the literals 1e-6 / 20 of :725.  1 <= n <= 31 in this build.
- * workspace: bx_prom_workspace_bytes(B, N) bytes (work queue + per-sample forcing data; contents
- * ignored, overwritten).                                                                         */
-long long bx_prom_workspace_bytes(int B, int N);
+ * tol, kmax: the literals 1e-6 / 20 of :725.  1 <= n <= 240 (the reference's stored truncations have
+ * 9 ... 227 modes, POD/modes/): n <= 31 runs one warp per trajectory with Phi in shared memory, n >= 32
+ * one CTA per trajectory with Phi streamed from L2 and a blocked LU of the reduced system.
+ * workspace: bx_prom_workspace_bytes(B, N, n) bytes (work queue, per-sample forcing data and, for
+ * large n, one reduced system per resident CTA; contents ignored, overwritten).                  */
+long long bx_prom_workspace_bytes(int B, int N, int n);
 int bx_prom_trajectories(int B, int N, int n, int nsteps, const double *X, const double *u0,
                          int u0_batched, const double *mu1, const double *mu2, double At, double E,
                          const double *Phi, int projection, double tol, int kmax,

@@ -22,7 +22,7 @@ def _phi(tol, n=None):
     return np.ascontiguousarray(Phi if n is None else Phi[:, :n])
 
 
-@pytest.mark.parametrize("n,proj", [(28, "LSPG"), (28, "Galerkin"), (9, "LSPG")])
+@pytest.mark.parametrize("n,proj", [(28, "LSPG"), (28, "Galerkin"), (9, "LSPG"), (40, "LSPG"), (40, "Galerkin")])
 def test_legacy_prom_vs_reference_run(n, proj, golden, fem512):
     g = golden("prom_short.npz")
     Phi = _phi("1e-03", n) if n != 9 else _phi("1e-02")
@@ -44,7 +44,13 @@ def test_alias_and_bad_projection(fem512):
 @pytest.mark.parametrize("name", ["U_PROM_tol_1e-02_mu1_4.750_mu2_0.0200_lspg",
                                   "U_PROM_tol_1e-02_mu1_5.190_mu2_0.0260_galerkin",
                                   "U_PROM_tol_4e-03_mu1_4.750_mu2_0.0200_galerkin",
-                                  "U_PROM_tol_4e-03_mu1_4.560_mu2_0.0190_lspg"])
+                                  "U_PROM_tol_4e-03_mu1_4.560_mu2_0.0190_lspg",
+                                  # 40 and 96 modes: the one-CTA-per-trajectory kernel (bx_prom_cta.cu);
+                                  # tol 1e-03 / LSPG / (4.75, 0.02) is what POD/Results_thesis/prom_pod.py runs as shipped
+                                  "U_PROM_tol_1e-03_mu1_4.750_mu2_0.0200_lspg",
+                                  "U_PROM_tol_1e-03_mu1_5.190_mu2_0.0260_galerkin",
+                                  "U_PROM_tol_1e-04_mu1_4.560_mu2_0.0190_lspg",
+                                  "U_PROM_tol_1e-04_mu1_4.750_mu2_0.0200_galerkin"])
 def test_stored_fixture_full_500_steps(name, golden, fem512):
     g = golden("prom_fixtures.npz")
     parts = name.split("_")
@@ -79,6 +85,42 @@ def test_sizes_vs_oracle(N, n, proj, oracle):
         Uo, ito = oracle.pod_prom_burgers(X, 0.05, 6, np.ones(N), mu1[b], 0.0, mu2[b], Phi, proj)
         assert np.array_equal(it[b], ito), (b, it[b], ito)
         assert rel_l2_per_step(U[b].T, Uo) <= TOL, b
+
+
+def _big_basis(oracle, X, n):
+    """n POD modes of six short oracle FOM trajectories (486 snapshots) on the mesh X."""
+    N = X.size
+    mu1 = np.linspace(4.3, 5.4, 6); mu2 = np.linspace(0.016, 0.029, 6)
+    U, _ = oracle.fom_burgers_batch(X, 0.05, 80, np.ones(N), mu1, 0.0, mu2)
+    Us = np.linalg.svd(U.reshape(-1, N).T, full_matrices=False)[0]
+    return np.ascontiguousarray(Us[:, :n])
+
+
+@pytest.mark.parametrize("N,n", [(512, 32), (300, 47), (512, 64), (1024, 72), (512, 129), (512, 160), (512, 227),
+                                 (512, 240)])
+@pytest.mark.parametrize("proj", ["LSPG", "Galerkin"])
+def test_large_basis_vs_oracle(N, n, proj, oracle):
+    """n >= 32 modes: one CTA per trajectory, Phi streamed from L2, blocked LU (reduced system in shared memory
+    up to n ~ 140, in an L2-resident scratch beyond); several trajectories so the sample queue is exercised."""
+    import burgers_b200
+    X = np.linspace(0.0, 100.0 * (N - 1) / 511.0, N)
+    fem = burgers_b200.FEMBurgers(X)
+    Phi = _big_basis(oracle, X, n)
+    mu1 = np.array([4.4, 5.2, 4.75]); mu2 = np.array([0.017, 0.028, 0.02])
+    U, it = fem.pod_prom_burgers_batch(0.05, 5, np.ones(N), mu1, 0.0, mu2, Phi, proj)
+    U = U.cpu().numpy(); it = it.cpu().numpy()
+    for b in range(3):
+        Uo, ito = oracle.pod_prom_burgers(X, 0.05, 5, np.ones(N), mu1[b], 0.0, mu2[b], Phi, proj)
+        assert np.array_equal(it[b], ito), (b, it[b], ito)
+        assert rel_l2_per_step(U[b].T, Uo) <= TOL, b
+
+
+def test_too_many_modes_is_an_error(oracle, fem512):
+    import burgers_b200
+    X, _ = oracle.mesh(512)
+    Phi = np.linalg.qr(np.random.default_rng(0).standard_normal((512, 241)))[0]
+    with pytest.raises(burgers_b200.BurgersB200Error):
+        fem512.pod_prom_burgers_batch(0.05, 1, np.ones(512), [4.75], 0.0, [0.02], Phi, "LSPG")
 
 
 def test_ragged_batch_batched_u0_and_empty(oracle, fem512):

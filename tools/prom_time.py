@@ -11,7 +11,12 @@ proj = sys.argv[3] if len(sys.argv) > 3 else "LSPG"
 steps = int(sys.argv[4]) if len(sys.argv) > 4 else 500
 X = np.linspace(0, 100, 512)
 fem = burgers_b200.FEMBurgers(X)
-Phi = np.ascontiguousarray(np.load(os.path.join(os.path.dirname(__file__), "..", "tests", "golden", "Phi_tol_1e-03.npy"))[:, :n])
+_g = os.path.join(os.path.dirname(__file__), "..", "tests", "golden")
+if n <= 96:   # the reference's stored POD modes (POD/modes/U_modes_tol_*.npy: 40 and 96 columns)
+    Phi = np.ascontiguousarray(np.load(os.path.join(_g, "Phi_tol_1e-03.npy" if n <= 40 else "Phi_tol_1e-04.npy"))[:, :n])
+else:         # larger bases: POD modes of a few oracle-free GPU FOM trajectories
+    Us, _ = fem.fom_burgers_batch(0.05, 80, np.ones(512), np.linspace(4.3, 5.4, 6), 0.0, np.linspace(0.016, 0.029, 6))
+    Phi = np.ascontiguousarray(np.linalg.svd(Us.reshape(-1, 512).T.cpu().numpy(), full_matrices=False)[0][:, :n])
 g = int(round(B ** 0.5))
 mu1, mu2 = sweep.parameter_grid(g, B // g)
 mu1 = torch.from_numpy(mu1).cuda(); mu2 = torch.from_numpy(mu2).cuda()
