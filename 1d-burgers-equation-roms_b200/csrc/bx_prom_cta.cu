@@ -100,7 +100,38 @@ __device__ __forceinline__ void cp_async8(double *dst, const double *src, bool o
     const unsigned sz = ok ? 8u : 0u;
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(sz) : "memory");
 }
+__device__ __forceinline__ void cp_async16(double *dst, const double *src, bool ok) {
+    const unsigned sz = ok ? 16u : 0u;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(sz) : "memory");
+}
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+// J = A Phi for the KC nodes of one chunk (row kk of the chunk by warp kk mod W, MC columns per lane), R as
+// column n, and the partial q0 += Phi^T U_k of the same rows.  ph: staged Phi rows (node c KC - 1 first).
+template <int MC>
+__device__ __forceinline__ void prom_cta_J(const double *ph, double *Jc, const double *s_ra, const double *s_rb,
+                                           const double *s_rc, const double *s_rR, const double *s_u, int c, int KC,
+                                           int W, int warp, int lane, int N, int n, int NC, int ldp, int S, int lgS,
+                                           bool with_q0, double (&q0acc)[8]) {
+    for (int kk = warp; kk < KC; kk += W) {
+        const int i = c * KC + kk;
+        const double ra = s_ra[i], rb = s_rb[i], rcc = s_rc[i], rR = s_rR[i];
+        const double ui = (with_q0 && i < N) ? s_u[sk(i, S, lgS)] : 0.0;
+        const double *r0 = ph + kk * ldp + lane;
+        double *jr = Jc + kk * ldp + lane;
+#pragma unroll
+        for (int m = 0; m < MC; ++m) {
+            const int j = lane + 32 * m;
+            if (j < NC) {
+                const double pm = r0[32 * m], p0 = r0[ldp + 32 * m], pp = r0[2 * ldp + 32 * m];
+                double v = fma(ra, pm, fma(rb, p0, rcc * pp));
+                if (j == n) v = rR;
+                jr[32 * m] = v;
+                q0acc[m] = fma(p0, ui, q0acc[m]);
+            }
+        }
+    }
+}
 
 template <bool LSPG>
 __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCtaParams p) {
@@ -132,6 +163,7 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
     rc.N = N; rc.S = S; rc.lgS = lgS;
 
     const int mcols = (NC + 31) >> 5;   // columns per lane in the J pass (<= 8)
+    const bool vec2 = (n & 1) == 0 && (reinterpret_cast<unsigned long long>(p.Phi) & 15ull) == 0;
 
     for (;;) {
         __syncthreads();
@@ -185,29 +217,23 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                         const int i = c * KC - 1 + r;
                         const bool rok = i >= 0 && i < N;
                         const double *src = p.Phi + (size_t)(rok ? i : 0) * n;
-                        for (int j = lane; j < NC; j += 32) cp_async8(dst + r * ldp + j, src + (j < n ? j : 0), rok && j < n);
+                        double *d = dst + r * ldp;
+                        if (vec2) {   // n even: rows are 16-byte aligned
+                            for (int j = 2 * lane; j < NC; j += 64) cp_async16(d + j, src + (j < n ? j : 0), rok && j < n);
+                        } else {
+                            for (int j = lane; j < NC; j += 32) cp_async8(d + j, src + (j < n ? j : 0), rok && j < n);
+                        }
                     }
                 };
                 auto compute_J = [&](int c, bool with_q0) {
                     const double *ph = s_phi + (c % 3) * lay.phisz;
                     double *Jc = s_J + (c & 1) * lay.Jsz;
-                    for (int kk = warp; kk < KC; kk += W) {
-                        const int i = c * KC + kk;
-                        const double ra = s_ra[i], rb = s_rb[i], rcc = s_rc[i], rR = s_rR[i];
-                        const double ui = (with_q0 && i < N) ? s_u[sk(i, S, lgS)] : 0.0;
-                        const double *r0 = ph + kk * ldp;
-#pragma unroll
-                        for (int m = 0; m < 8; ++m) {
-                            const int j = lane + 32 * m;
-                            if (m < mcols && j < NC) {
-                                const double pm = r0[j], p0 = r0[ldp + j], pp = r0[2 * ldp + j];
-                                double v = fma(ra, pm, fma(rb, p0, rcc * pp));
-                                if (j == n) v = rR;
-                                Jc[kk * ldp + j] = v;
-                                q0acc[m] = fma(p0, ui, q0acc[m]);
-                            }
-                        }
-                    }
+                    if (mcols <= 2)
+                        prom_cta_J<2>(ph, Jc, s_ra, s_rb, s_rc, s_rR, s_u, c, KC, W, warp, lane, N, n, NC, ldp, S, lgS, with_q0, q0acc);
+                    else if (mcols <= 4)
+                        prom_cta_J<4>(ph, Jc, s_ra, s_rb, s_rc, s_rR, s_u, c, KC, W, warp, lane, N, n, NC, ldp, S, lgS, with_q0, q0acc);
+                    else
+                        prom_cta_J<8>(ph, Jc, s_ra, s_rb, s_rc, s_rR, s_u, c, KC, W, warp, lane, N, n, NC, ldp, S, lgS, with_q0, q0acc);
                 };
 
                 for (int pass = 0; pass < p.passes; ++pass) {
@@ -447,19 +473,35 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                     for (int ww = 0; ww < W; ++ww) { a += s_red2[2 * ww]; b += s_red2[2 * ww + 1]; }
                     err = sqrt(a) / sqrt(b);
                 }
-                for (int i0 = warp * 4; i0 < N; i0 += W * 4) {
-                    double v[4] = {0.0, 0.0, 0.0, 0.0};
+                for (int i0 = warp * 8; i0 < N; i0 += W * 8) {
+                    double v[8];
+#pragma unroll
+                    for (int r = 0; r < 8; ++r) v[r] = 0.0;
                     for (int j = lane; j < n; j += 32) {
                         const double qj = s_q[j];
+                        const double *pj = p.Phi + (size_t)i0 * n + j;
 #pragma unroll
-                        for (int r = 0; r < 4; ++r)
-                            if (i0 + r < N) v[r] = fma(p.Phi[(size_t)(i0 + r) * n + j], qj, v[r]);
+                        for (int r = 0; r < 8; ++r)
+                            if (i0 + r < N) v[r] = fma(pj[(size_t)r * n], qj, v[r]);
+                    }
+                    // recursive halving over lane bits 4, 3, 2, then bits 1, 0: lane 4 g + t ends with node i0 + g
+                    double w4[4], w2[2];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const double send = (g & 4) ? v[j] : v[j + 4];
+                        const double keep = (g & 4) ? v[j + 4] : v[j];
+                        w4[j] = keep + shfl_xor(send, 16);
                     }
 #pragma unroll
-                    for (int r = 0; r < 4; ++r) {
-                        const double sum = warp_sum(v[r]);
-                        if (lane == 0 && i0 + r < N) s_u[sk(i0 + r, S, lgS)] = sum;
+                    for (int j = 0; j < 2; ++j) {
+                        const double send = (g & 2) ? w4[j] : w4[j + 2];
+                        const double keep = (g & 2) ? w4[j + 2] : w4[j];
+                        w2[j] = keep + shfl_xor(send, 8);
                     }
+                    double w1 = ((g & 1) ? w2[1] : w2[0]) + shfl_xor((g & 1) ? w2[0] : w2[1], 4);
+                    w1 += shfl_xor(w1, 2);
+                    w1 += shfl_xor(w1, 1);
+                    if (t == 0 && i0 + g < N) s_u[sk(i0 + g, S, lgS)] = w1;
                 }
                 __syncthreads();
                 ++k;
@@ -485,7 +527,7 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
     p.ldp = p.NC + 4;                 // 4 mod 8: conflict-free DMMA fragment loads
     p.ldm = (n + 1) | 1;              // odd, >= n + 1
     p.units = projection == BX_LSPG ? p.NBu * (p.NBu + 1) / 2 : p.NBu * p.NBu;
-    int W = 4;
+    int W = 8;   // at least 8 warps: staging, the J pass and the lift are per-warp instruction bound
     while (W < PC_MAXW && (W * PC_UB < p.units || W * 32 < p.NC)) W *= 2;
     p.passes = (p.units + W * PC_UB - 1) / (W * PC_UB);
     p.lgS = 3;
@@ -494,19 +536,31 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
     BX_CUDA(cudaGetDevice(&dev));
     BX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     BX_CUDA(cudaDeviceGetAttribute(&maxsm, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
-    // largest chunk that fits, reduced system in shared memory if possible
+    // chunk size: the one that keeps the most warps resident (2048 threads, 228 KB per SM), larger chunks on a
+    // tie; reduced system in shared memory if it fits at all
     static const int kcs[3] = {32, 16, 8};
     PromCtaSmem lay;
     bool found = false;
     for (int mg = 0; mg < 2 && !found; ++mg) {
-        for (int ki = 0; ki < 3 && !found; ++ki) {
-            if (mg == 0 && kcs[ki] == 32 && n > 64) continue;   // leave room for a second CTA per SM
-            p.KC = kcs[ki];
+        int best_occ = 0, best_kc = 0;
+        for (int ki = 0; ki < 3; ++ki) {
+            const int kc = kcs[ki];
+            const int nch = (N + kc - 1) / kc;
+            const PromCtaSmem l = PromCtaSmem::make(N, n, p.NC, p.ldp, p.ldm, kc, nch * kc, p.lgS, W, mg ? 0 : 1);
+            const long long bytes = (long long)l.total * (long long)sizeof(double);
+            if (bytes > (long long)maxsm) continue;
+            int o = (int)(233472LL / (bytes + 1024));
+            if (o > 2048 / (W * 32)) o = 2048 / (W * 32);
+            if (o > 4) o = 4;
+            if (o > best_occ) { best_occ = o; best_kc = kc; }
+        }
+        if (best_occ > 0) {
+            found = true;
+            p.KC = best_kc;
             p.nchunks = (N + p.KC - 1) / p.KC;
             p.NPad = p.nchunks * p.KC;
             p.mat_global = mg;
             lay = PromCtaSmem::make(N, n, p.NC, p.ldp, p.ldm, p.KC, p.NPad, p.lgS, W, mg ? 0 : 1);
-            found = (long long)lay.total * (long long)sizeof(double) <= (long long)maxsm;
         }
     }
     // resident CTAs per SM can never exceed what shared memory allows (1 KB reserved per CTA)
