@@ -4,7 +4,8 @@
 //
 // One CTA (4, 8 or 16 warps) integrates one trajectory; CTAs pull samples from an atomic queue.  The basis
 // Phi (N x n, up to 0.9 MB) no longer fits next to the work tiles, so it streams from L2 in chunks of KC nodes
-// (cp.async, three-deep ring); the state, the bands and the n x n reduced system stay in shared memory for the
+// (a zero-padded N x NC copy of Phi in the workspace, rows moved by 1-D bulk copies of the TMA engine into a
+// three-deep mbarrier ring); the state, the bands and the n x n reduced system stay in shared memory for the
 // whole trajectory (the reduced system moves to an L2-resident scratch when it exceeds what is left, n >~ 140).
 //
 // One nonlinear iteration (:726-781):
@@ -31,7 +32,6 @@ int launch_prom_forcing(int B, int N, const double *X, const double *mu2, double
 
 constexpr int PC_UB = 4;        // 16 x 16 output units a warp accumulates per pass (32 FP64 accumulators)
 constexpr int PC_MAXW = 16;
-constexpr int PC_NMAX = 240;    // NC = 16 ceil((n+1)/16) <= 256 = 8 columns per lane in the J pass
 
 struct PromCtaParams {
     int B, N, n, nsteps, kmax;
@@ -44,6 +44,8 @@ struct PromCtaParams {
     const double *mu2;
     double At, E, tol;
     const double *Phi;
+    double *Phip;        // workspace: zero-padded copy of Phi, (NPad + 2) x NC, row 0 = node -1
+    int CG, RR, RPT;     // J pass: warps per row run, row runs, rows per thread
     double *atf, *hfs;
     double *mat_ws;      // per-CTA reduced system when it does not fit in shared memory
     double *U;
@@ -53,7 +55,7 @@ struct PromCtaParams {
 
 // shared-memory carve-up (doubles), identical on host and device
 struct PromCtaSmem {
-    int h6, u, bn, hfs, ra, rb, rc, rR, q, q0, x, prow, cand, red2, ints, work, phi, J, L, red, mat, total;
+    int h6, u, bn, hfs, row, bar, q, q0, x, prow, cand, red2, ints, work, phi, J, L, red, mat, total;
     int arr, phisz, Jsz;
     __host__ __device__ static PromCtaSmem make(int N, int n, int NC, int ldp, int ldm, int KC, int NPad, int lgS,
                                                 int W, int mat_in_smem) {
@@ -65,10 +67,9 @@ struct PromCtaSmem {
         m.u = o; o += m.arr;
         m.bn = o; o += m.arr;
         m.hfs = o; o += m.arr;
-        m.ra = o; o += NPad;
-        m.rb = o; o += NPad;
-        m.rc = o; o += NPad;
-        m.rR = o; o += NPad;
+        o = (o + 1) & ~1;
+        m.row = o; o += 4 * NPad;           // {a, b, c, R} per node, 32-byte records
+        m.bar = o; o += 4;                  // 3 mbarriers
         m.q = o; o += NC;
         m.q0 = o; o += NC;
         m.x = o; o += NC;
@@ -96,41 +97,14 @@ struct PromCtaSmem {
     }
 };
 
-__device__ __forceinline__ void cp_async8(double *dst, const double *src, bool ok) {
-    const unsigned sz = ok ? 8u : 0u;
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(sz) : "memory");
-}
-__device__ __forceinline__ void cp_async16(double *dst, const double *src, bool ok) {
-    const unsigned sz = ok ? 16u : 0u;
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(sz) : "memory");
-}
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
-
-// J = A Phi for the KC nodes of one chunk (row kk of the chunk by warp kk mod W, MC columns per lane), R as
-// column n, and the partial q0 += Phi^T U_k of the same rows.  ph: staged Phi rows (node c KC - 1 first).
-template <int MC>
-__device__ __forceinline__ void prom_cta_J(const double *ph, double *Jc, const double *s_ra, const double *s_rb,
-                                           const double *s_rc, const double *s_rR, const double *s_u, int c, int KC,
-                                           int W, int warp, int lane, int N, int n, int NC, int ldp, int S, int lgS,
-                                           bool with_q0, double (&q0acc)[8]) {
-    for (int kk = warp; kk < KC; kk += W) {
-        const int i = c * KC + kk;
-        const double ra = s_ra[i], rb = s_rb[i], rcc = s_rc[i], rR = s_rR[i];
-        const double ui = (with_q0 && i < N) ? s_u[sk(i, S, lgS)] : 0.0;
-        const double *r0 = ph + kk * ldp + lane;
-        double *jr = Jc + kk * ldp + lane;
-#pragma unroll
-        for (int m = 0; m < MC; ++m) {
-            const int j = lane + 32 * m;
-            if (j < NC) {
-                const double pm = r0[32 * m], p0 = r0[ldp + 32 * m], pp = r0[2 * ldp + 32 * m];
-                double v = fma(ra, pm, fma(rb, p0, rcc * pp));
-                if (j == n) v = rR;
-                jr[32 * m] = v;
-                q0acc[m] = fma(p0, ui, q0acc[m]);
-            }
-        }
-    }
+// zero-padded copy of Phi: row ip = node ip - 1, NC columns
+__global__ void __launch_bounds__(256) prom_cta_pad_kernel(int N, int n, int NC, int rows, const double *Phi,
+                                                           double *Phip) {
+    const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
+    if (idx >= (long long)rows * NC) return;
+    const int ip = (int)(idx / NC), j = (int)(idx - (long long)ip * NC);
+    const int i = ip - 1;
+    Phip[idx] = (i >= 0 && i < N && j < n) ? Phi[(size_t)i * n + j] : 0.0;
 }
 
 template <bool LSPG>
@@ -143,7 +117,8 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
     const int t = lane & 3, g = lane >> 2;
     const PromCtaSmem lay = PromCtaSmem::make(N, n, NC, ldp, ldm, KC, p.NPad, lgS, W, p.mat_global ? 0 : 1);
     double *s_h6 = smem + lay.h6, *s_u = smem + lay.u, *s_bn = smem + lay.bn, *s_hfs = smem + lay.hfs;
-    double *s_ra = smem + lay.ra, *s_rb = smem + lay.rb, *s_rc = smem + lay.rc, *s_rR = smem + lay.rR;
+    double2 *s_row = reinterpret_cast<double2 *>(smem + lay.row);
+    uint64_t *s_bar = reinterpret_cast<uint64_t *>(smem + lay.bar);
     double *s_q = smem + lay.q, *s_q0 = smem + lay.q0, *s_x = smem + lay.x, *s_prow = smem + lay.prow;
     double *s_cand = smem + lay.cand, *s_red2 = smem + lay.red2;
     int *s_pivrow = reinterpret_cast<int *>(smem + lay.ints);
@@ -154,6 +129,11 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
 
     // ---- CTA prologue: mesh constants, halo words ---------------------------------------------
     for (int i = tid; i < lay.arr; i += T) { s_h6[i] = 0.0; s_u[i] = 0.0; s_bn[i] = 0.0; s_hfs[i] = 0.0; }
+    if (tid == 0) {
+        for (int b = 0; b < 3; ++b) mbar_init(&s_bar[b], 1);
+        fence_mbar_init();
+    }
+    unsigned gchunk = 0;   // chunks staged so far (ring slot = gchunk % 3, parity = (gchunk / 3) & 1)
     __syncthreads();
     for (int e = tid; e <= N - 2; e += T) s_h6[sk(e, S, lgS)] = (p.X[e + 1] - p.X[e]) / 6.0;
 
@@ -162,8 +142,10 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
     rc.a6 = p.At / 6.0; rc.c1 = 1.5 * p.At; rc.ate = p.At * p.E; rc.has_e = p.E != 0.0; rc.supg = true;
     rc.N = N; rc.S = S; rc.lgS = lgS;
 
-    const int mcols = (NC + 31) >> 5;   // columns per lane in the J pass (<= 8)
-    const bool vec2 = (n & 1) == 0 && (reinterpret_cast<unsigned long long>(p.Phi) & 15ull) == 0;
+    // J pass: thread = (column jcol, row run jrr); RPT consecutive rows per thread with a rolling 3-row window
+    const int jcol = (warp % p.CG) * 32 + lane, jrr = warp / p.CG;
+    const bool jact = jcol < NC && jrr < p.RR;
+    const int RPT = p.RPT;
 
     for (;;) {
         __syncthreads();
@@ -202,38 +184,47 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                     PromRow r;
                     if (i < N) r = prom_row(rc, i, sk(i, S, lgS));
                     else { r.a = 0.0; r.b = 0.0; r.c = 0.0; r.R = 0.0; }
-                    s_ra[i] = r.a; s_rb[i] = r.b; s_rc[i] = r.c; s_rR[i] = r.R;
+                    s_row[2 * i] = make_double2(r.a, r.b);
+                    s_row[2 * i + 1] = make_double2(r.c, r.R);
                 }
                 // (the barrier after the first staging below orders these writes before their readers)
 
                 // ================= phase B: J = A Phi, contraction (:756-762) ====================
-                double q0acc[8];
-#pragma unroll
-                for (int m = 0; m < 8; ++m) q0acc[m] = 0.0;
-
-                auto stage_phi = [&](int c) {
-                    double *dst = s_phi + (c % 3) * lay.phisz;
-                    for (int r = warp; r < KC + 2; r += W) {
-                        const int i = c * KC - 1 + r;
-                        const bool rok = i >= 0 && i < N;
-                        const double *src = p.Phi + (size_t)(rok ? i : 0) * n;
-                        double *d = dst + r * ldp;
-                        if (vec2) {   // n even: rows are 16-byte aligned
-                            for (int j = 2 * lane; j < NC; j += 64) cp_async16(d + j, src + (j < n ? j : 0), rok && j < n);
-                        } else {
-                            for (int j = lane; j < NC; j += 32) cp_async8(d + j, src + (j < n ? j : 0), rok && j < n);
-                        }
+                double q0acc = 0.0;
+                // stage the KC + 2 Phi rows of chunk c (global number gc): one bulk copy per row, issued by warp 0
+                auto stage_phi = [&](int c, unsigned gc) {
+                    if (warp == 0) {
+                        const unsigned slot = gc % 3u;
+                        fence_proxy_async();   // the ring aliases buffers the generic proxy wrote (L21 panel, partial q0)
+                        if (lane == 0) mbar_arrive_expect_tx(&s_bar[slot], (uint32_t)((KC + 2) * NC * 8));
+                        __syncwarp();
+                        double *dst = s_phi + slot * lay.phisz;
+                        const double *src = p.Phip + (size_t)c * KC * NC;
+                        for (int r = lane; r < KC + 2; r += 32)
+                            bulk_g2s(dst + r * ldp, src + (size_t)r * NC, (uint32_t)(NC * 8), &s_bar[slot]);
                     }
                 };
-                auto compute_J = [&](int c, bool with_q0) {
-                    const double *ph = s_phi + (c % 3) * lay.phisz;
-                    double *Jc = s_J + (c & 1) * lay.Jsz;
-                    if (mcols <= 2)
-                        prom_cta_J<2>(ph, Jc, s_ra, s_rb, s_rc, s_rR, s_u, c, KC, W, warp, lane, N, n, NC, ldp, S, lgS, with_q0, q0acc);
-                    else if (mcols <= 4)
-                        prom_cta_J<4>(ph, Jc, s_ra, s_rb, s_rc, s_rR, s_u, c, KC, W, warp, lane, N, n, NC, ldp, S, lgS, with_q0, q0acc);
-                    else
-                        prom_cta_J<8>(ph, Jc, s_ra, s_rb, s_rc, s_rR, s_u, c, KC, W, warp, lane, N, n, NC, ldp, S, lgS, with_q0, q0acc);
+                auto compute_J = [&](int c, unsigned gc, bool with_q0) {
+                    mbar_wait(&s_bar[gc % 3u], (gc / 3u) & 1u);
+                    if (jact) {
+                        const int kk0 = jrr * RPT;
+                        const double *ph = s_phi + (gc % 3u) * lay.phisz + kk0 * ldp + jcol;
+                        double *jr = s_J + (c & 1) * lay.Jsz + kk0 * ldp + jcol;
+                        const double2 *rw = s_row + 2 * (c * KC + kk0);
+                        const double *up = s_u + c * KC + kk0 + 2;   // sk(i) = i + 2 for 0 <= i < S
+                        double pm = ph[0], p0 = ph[ldp];
+                        const bool isR = jcol == n;
+#pragma unroll 4
+                        for (int q = 0; q < RPT; ++q) {
+                            const double pp = ph[(q + 2) * ldp];
+                            const double2 ab = rw[2 * q], cR = rw[2 * q + 1];
+                            double v = fma(ab.x, pm, fma(ab.y, p0, cR.x * pp));
+                            if (isR) v = cR.y;
+                            jr[q * ldp] = v;
+                            if (with_q0) q0acc = fma(p0, up[q], q0acc);
+                            pm = p0; p0 = pp;
+                        }
+                    }
                 };
 
                 for (int pass = 0; pass < p.passes; ++pass) {
@@ -259,17 +250,16 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                         udiag[s] = Iu == Ju;
                         offA[s] = Iu * 16 + g; offB[s] = Ju * 16 + g;
                     }
-                    stage_phi(0);
-                    if (p.nchunks > 1) stage_phi(1);
-                    cp_async_wait_all();
-                    __syncthreads();
-                    compute_J(0, pass == 0);
+                    __syncthreads();   // rows of phase A written; ring slots free
+                    stage_phi(0, gchunk);
+                    if (p.nchunks > 1) stage_phi(1, gchunk + 1);
+                    compute_J(0, gchunk, pass == 0);
                     __syncthreads();
                     for (int c = 0; c < p.nchunks; ++c) {
-                        if (c + 2 < p.nchunks) stage_phi(c + 2);
-                        if (c + 1 < p.nchunks) compute_J(c + 1, pass == 0);
+                        if (c + 2 < p.nchunks) stage_phi(c + 2, gchunk + c + 2);
+                        if (c + 1 < p.nchunks) compute_J(c + 1, gchunk + c + 1, pass == 0);
                         const double *Jc = s_J + (c & 1) * lay.Jsz;
-                        const double *Ac = LSPG ? Jc : s_phi + (c % 3) * lay.phisz + ldp;
+                        const double *Ac = LSPG ? Jc : s_phi + ((gchunk + c) % 3u) * lay.phisz + ldp;
                         for (int ks = 0; ks < KC; ks += 4) {
                             const int ro = (ks + t) * ldp;
 #pragma unroll
@@ -284,9 +274,9 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                                 }
                             }
                         }
-                        cp_async_wait_all();
                         __syncthreads();
                     }
+                    gchunk += (unsigned)p.nchunks;
                     // accumulator tiles -> [Ar | br]; column n = br
 #pragma unroll
                     for (int s = 0; s < PC_UB; ++s) {
@@ -306,16 +296,12 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                         }
                     }
                 }
-                // q0 = Phi^T U_k (:770): per-warp partials summed in warp order
-#pragma unroll
-                for (int m = 0; m < 8; ++m) {
-                    const int j = lane + 32 * m;
-                    if (m < mcols && j < NC) s_red[warp * NC + j] = q0acc[m];
-                }
+                // q0 = Phi^T U_k (:770): per-row-run partials summed in run order
+                if (jact) s_red[jrr * NC + jcol] = q0acc;
                 __syncthreads();
                 if (tid < NC) {
                     double sum = 0.0;
-                    for (int w = 0; w < W; ++w) sum += s_red[w * NC + tid];
+                    for (int w = 0; w < p.RR; ++w) sum += s_red[w * NC + tid];
                     s_q0[tid] = tid < n ? sum : 0.0;
                 }
                 __syncthreads();
@@ -477,12 +463,14 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                     double v[8];
 #pragma unroll
                     for (int r = 0; r < 8; ++r) v[r] = 0.0;
-                    for (int j = lane; j < n; j += 32) {
-                        const double qj = s_q[j];
-                        const double *pj = p.Phi + (size_t)i0 * n + j;
+                    for (int j = 2 * lane; j < NC; j += 64) {   // padded rows: columns >= n and nodes >= N are zero
+                        const double q0j = s_q[j], q1j = s_q[j + 1];
+                        const double2 *pj = reinterpret_cast<const double2 *>(p.Phip + (size_t)(i0 + 1) * NC + j);
 #pragma unroll
-                        for (int r = 0; r < 8; ++r)
-                            if (i0 + r < N) v[r] = fma(pj[(size_t)r * n], qj, v[r]);
+                        for (int r = 0; r < 8; ++r) {
+                            const double2 ph2 = pj[(size_t)r * (NC / 2)];
+                            v[r] = fma(ph2.x, q0j, fma(ph2.y, q1j, v[r]));
+                        }
                     }
                     // recursive halving over lane bits 4, 3, 2, then bits 1, 0: lane 4 g + t ends with node i0 + g
                     double w4[4], w2[2];
@@ -563,12 +551,20 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
             lay = PromCtaSmem::make(N, n, p.NC, p.ldp, p.ldm, p.KC, p.NPad, p.lgS, W, mg ? 0 : 1);
         }
     }
+    if (found) {
+        p.CG = 1;
+        while (p.CG * 32 < p.NC) p.CG *= 2;
+        p.RR = W / p.CG;                    // W >= NC / 32 and both are powers of two
+        while (p.KC % p.RR) p.RR /= 2;
+        p.RPT = p.KC / p.RR;
+    }
     // resident CTAs per SM can never exceed what shared memory allows (1 KB reserved per CTA)
     int occ_bound = found ? (int)(233472LL / ((long long)lay.total * (long long)sizeof(double) + 1024)) : 1;
     if (occ_bound < 1) occ_bound = 1;
     if (occ_bound > 4) occ_bound = 4;
     if (mat_bytes_out) {   // workspace query: one reduced system per resident CTA when it lives in global memory
         *mat_bytes_out = (found && p.mat_global) ? (long long)sms * occ_bound * (long long)n * p.ldm * (long long)sizeof(double) : 0;
+        *mat_bytes_out += (long long)(N + 34) * p.NC * (long long)sizeof(double);   // padded Phi
         return BX_OK;
     }
     if (!found) {
@@ -581,7 +577,8 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
     p.counter = static_cast<unsigned int *>(workspace);
     p.atf = reinterpret_cast<double *>(static_cast<char *>(workspace) + 256);
     p.hfs = p.atf + (size_t)B * N;
-    p.mat_ws = reinterpret_cast<double *>(static_cast<char *>(workspace) + mat_offset_bytes);
+    p.Phip = reinterpret_cast<double *>(static_cast<char *>(workspace) + mat_offset_bytes);
+    p.mat_ws = p.Phip + (size_t)(N + 34) * p.NC;
     const size_t smem = sizeof(double) * (size_t)lay.total;
     int occ = 0;
     if (projection == BX_LSPG) {
@@ -602,6 +599,11 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
     {
         const int rcf = launch_prom_forcing(B, N, X, mu2, At, p.atf, p.hfs, st);
         if (rcf != BX_OK) return rcf;
+    }
+    {
+        const int rows = p.NPad + 2;   // <= N + 33
+        prom_cta_pad_kernel<<<(unsigned)(((long long)rows * p.NC + 255) / 256), 256, 0, st>>>(N, n, p.NC, rows, Phi, p.Phip);
+        BX_LAUNCH_CHECK();
     }
     if (projection == BX_LSPG) prom_cta_kernel<true><<<(unsigned)ctas, W * 32, smem, st>>>(p);
     else prom_cta_kernel<false><<<(unsigned)ctas, W * 32, smem, st>>>(p);
