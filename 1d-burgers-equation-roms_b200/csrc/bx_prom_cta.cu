@@ -79,16 +79,16 @@ struct PromCtaSmem {
         m.ints = o; o += NC + NC / 4 + 8;   // pivrow[NC] (int), act[NC] (int) -> NC doubles; cnt[W] + misc
         o = (o + 1) & ~1;
         m.work = o;
-        // work region: chunk ring during the contraction, packed L21 panel / reductions afterwards
+        // chunk ring
         m.phisz = (KC + 2) * ldp;
         m.Jsz = KC * ldp;
         m.phi = o; m.J = o + 3 * m.phisz;
-        int wsz = 3 * m.phisz + 2 * m.Jsz;
-        m.L = o;                             // NC x 8, 16-byte aligned rows
-        m.red = o;                           // W x NC partial q0
-        if (wsz < NC * 8) wsz = NC * 8;
-        if (wsz < W * NC) wsz = W * NC;
-        o += wsz;
+        o += 3 * m.phisz + 2 * m.Jsz;
+        o = (o + 1) & ~1;
+        // the ring is refilled for the next contraction while the LU runs, so these do not alias it
+        m.L = o;                             // packed L21 panel, NC x 8, 16-byte aligned rows
+        m.red = o;                           // partial q0 per row run (<= 8 x NC), dead before the LU starts
+        o += NC * 8;
         o = (o + 1) & ~1;
         m.mat = o;
         if (mat_in_smem) o += n * ldm;
@@ -147,12 +147,34 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
     const bool jact = jcol < NC && jrr < p.RR;
     const int RPT = p.RPT;
 
+    // stage the KC + 2 Phi rows of chunk c (global number gc): one bulk copy per row, issued by warp 0
+    auto stage_phi = [&](int c, unsigned gc) {
+        if (warp == 0) {
+            const unsigned slot = gc % 3u;
+            fence_proxy_async();   // the ring aliases buffers the generic proxy wrote (L21 panel, partial q0)
+            if (lane == 0) mbar_arrive_expect_tx(&s_bar[slot], (uint32_t)((KC + 2) * NC * 8));
+            __syncwarp();
+            double *dst = s_phi + slot * lay.phisz;
+            const double *src = p.Phip + (size_t)c * KC * NC;
+            for (int r = lane; r < KC + 2; r += 32)
+                bulk_g2s(dst + r * ldp, src + (size_t)r * NC, (uint32_t)(NC * 8), &s_bar[slot]);
+        }
+    };
+    // invariant: the first two chunks of the next contraction pass are always in flight (Phi does not depend on
+    // the state), so a pass never starts with an exposed L2 round trip
+    stage_phi(0, gchunk);
+    if (p.nchunks > 1) stage_phi(1, gchunk + 1);
+
     for (;;) {
         __syncthreads();
         if (tid == 0) s_cnt[W] = (int)atomicAdd(p.counter, 1u);
         __syncthreads();
         const int smp = s_cnt[W];
-        if (smp >= p.B) break;
+        if (smp >= p.B) {   // drain the two chunks in flight before the CTA gives up its shared memory
+            mbar_wait(&s_bar[gchunk % 3u], (gchunk / 3u) & 1u);
+            if (p.nchunks > 1) mbar_wait(&s_bar[(gchunk + 1) % 3u], ((gchunk + 1) / 3u) & 1u);
+            break;
+        }
         rc.mu1 = p.mu1[smp];
         const double *atf = p.atf + (size_t)smp * N;
         double *Us = p.U + (long long)smp * (long long)(p.nsteps + 1) * N;
@@ -191,19 +213,6 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
 
                 // ================= phase B: J = A Phi, contraction (:756-762) ====================
                 double q0acc = 0.0;
-                // stage the KC + 2 Phi rows of chunk c (global number gc): one bulk copy per row, issued by warp 0
-                auto stage_phi = [&](int c, unsigned gc) {
-                    if (warp == 0) {
-                        const unsigned slot = gc % 3u;
-                        fence_proxy_async();   // the ring aliases buffers the generic proxy wrote (L21 panel, partial q0)
-                        if (lane == 0) mbar_arrive_expect_tx(&s_bar[slot], (uint32_t)((KC + 2) * NC * 8));
-                        __syncwarp();
-                        double *dst = s_phi + slot * lay.phisz;
-                        const double *src = p.Phip + (size_t)c * KC * NC;
-                        for (int r = lane; r < KC + 2; r += 32)
-                            bulk_g2s(dst + r * ldp, src + (size_t)r * NC, (uint32_t)(NC * 8), &s_bar[slot]);
-                    }
-                };
                 auto compute_J = [&](int c, unsigned gc, bool with_q0) {
                     mbar_wait(&s_bar[gc % 3u], (gc / 3u) & 1u);
                     if (jact) {
@@ -250,9 +259,7 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                         udiag[s] = Iu == Ju;
                         offA[s] = Iu * 16 + g; offB[s] = Ju * 16 + g;
                     }
-                    __syncthreads();   // rows of phase A written; ring slots free
-                    stage_phi(0, gchunk);
-                    if (p.nchunks > 1) stage_phi(1, gchunk + 1);
+                    __syncthreads();   // rows of phase A written
                     compute_J(0, gchunk, pass == 0);
                     __syncthreads();
                     for (int c = 0; c < p.nchunks; ++c) {
@@ -277,6 +284,8 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                         __syncthreads();
                     }
                     gchunk += (unsigned)p.nchunks;
+                    stage_phi(0, gchunk);   // next pass / iteration / sample: ring slots are free after the barrier above
+                    if (p.nchunks > 1) stage_phi(1, gchunk + 1);
                     // accumulator tiles -> [Ar | br]; column n = br
 #pragma unroll
                     for (int s = 0; s < PC_UB; ++s) {
