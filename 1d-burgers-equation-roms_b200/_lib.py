@@ -42,6 +42,7 @@ SIGNATURES = {
                                         P, P, c_int, c_double, c_int, P, P, P, P]),
     "bx_gram_workspace_bytes": (c_longlong, [c_int, c_longlong]),
     "bx_gram_accumulate": (c_int, [c_int, c_longlong, P, P, c_int, P, P]),
+    "bx_snapshots_to_reference_layout": (c_int, [c_int, c_int, c_int, P, P, P]),
 }
 
 _lib = None

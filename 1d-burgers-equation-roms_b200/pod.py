@@ -112,6 +112,18 @@ def pod_basis(snapshot_buffers, n_modes: int | None = None, group=None):
     return basis_from_gram(acc.G, n_modes)
 
 
+def load_snapshot_directory(directory, device=None, prefix="fem_simulation_"):
+    """POD/pod.py:80-82: every `fem_simulation_*.npy` (each (N, steps+1)) of a directory, as ONE CUDA
+    snapshot buffer (n_files*(steps+1), N) with the node axis last — the layout GramAccumulator.add and
+    pod_basis take.  Column order across files does not change S S^T."""
+    files = sorted(f for f in os.listdir(directory) if f.endswith(".npy") and f.startswith(prefix))
+    if not files:
+        raise FileNotFoundError(f"no {prefix}*.npy under {directory}")
+    dev = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+    blocks = [torch.from_numpy(np.ascontiguousarray(np.load(os.path.join(directory, f)).T)).to(dev) for f in files]
+    return torch.cat(blocks, dim=0).contiguous(), files
+
+
 def save_modes(U, s, tolerances_squared, snapshots_shape=None, directory="modes"):
     """POD/pod.py:68-78: one `U_modes_tol_{eps2:.0e}.npy` + `Singular_values_modes_tol_*.npy` per tolerance."""
     U = U.cpu().numpy() if isinstance(U, torch.Tensor) else np.asarray(U)

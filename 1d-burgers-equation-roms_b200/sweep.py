@@ -8,6 +8,12 @@
                           H2D of the parameters, fused trajectory kernel, D2H of the snapshots
                           into pinned buffers, chunk by chunk, copy overlapped with compute
   * snapshot_filename   — the reference's on-disk name (:52)
+  * to_reference_layout — device transpose (B, steps+1, N) -> (B, N, steps+1), the array the reference saves
+  * sweep_to_npy        — the whole training/testing stage: sweep on the GPU, one
+                          `fem_simulation_mu1_{:.3f}_mu2_{:.4f}.npy` of shape (N, steps+1) per sample (:52-53),
+                          transposed on the device, copied out through pinned buffers, written by a small
+                          thread pool while the next chunk integrates
+  * prom_filename       — POD/Results_thesis/prom_pod.py:60
 """
 from __future__ import annotations
 
@@ -31,6 +37,114 @@ def shard_range(n_samples: int, rank: int, world: int):
 
 def snapshot_filename(mu1: float, mu2: float) -> str:
     return f"fem_simulation_mu1_{mu1:.3f}_mu2_{mu2:.4f}.npy"
+
+
+def prom_filename(tol: float, mu1: float, mu2: float, projection: str) -> str:
+    """POD/Results_thesis/prom_pod.py:59-60."""
+    tag = "lspg" if projection.lower() == "lspg" else "galerkin"
+    return f"U_PROM_tol_{tol:.0e}_mu1_{mu1:.3f}_mu2_{mu2:.4f}_{tag}.npy"
+
+
+def to_reference_layout(fem, U: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+    """(B, steps+1, N) trajectory buffer -> (B, N, steps+1): per sample the (N, nTimeSteps+1) C-order array
+    FEMBurgers.fom_burgers returns and the drivers np.save (FEM/paper_training_stage.py:52-53)."""
+    from . import _lib
+    if not (U.is_cuda and U.dtype == torch.float64 and U.is_contiguous() and U.dim() == 3):
+        raise ValueError("U must be a contiguous CUDA float64 tensor (B, steps+1, N)")
+    B, rows, N = U.shape
+    Ur = out if out is not None else torch.empty((B, N, rows), dtype=torch.float64, device=U.device)
+    if tuple(Ur.shape) != (B, N, rows) or not Ur.is_contiguous() or Ur.dtype != torch.float64:
+        raise ValueError("out must be a contiguous float64 tensor (B, N, steps+1)")
+    lib = _lib.load()
+    for lo in range(0, B, 65535):
+        hi = min(B, lo + 65535)
+        _lib.check(lib.bx_snapshots_to_reference_layout(hi - lo, rows, N, U[lo:hi].data_ptr(), Ur[lo:hi].data_ptr(),
+                                                        torch.cuda.current_stream().cuda_stream),
+                   "bx_snapshots_to_reference_layout")
+    return Ur
+
+
+def _write_npy(path: str, arr: np.ndarray):
+    """np.save without the extra copy: version-1.0 header + the raw C-order bytes."""
+    with open(path, "wb") as f:
+        np.lib.format.write_array_header_1_0(f, {"descr": np.lib.format.dtype_to_descr(arr.dtype),
+                                                 "fortran_order": False, "shape": arr.shape})
+        f.write(memoryview(arr).cast("B"))
+
+
+def sweep_to_npy(fem, directory, At, nTimeSteps, u0, mu1, mu2, E=0.0, chunk=256, method="fom_burgers",
+                 name=snapshot_filename, writers=4, **kwargs):
+    """Run `method` (a `*_batch` trajectory method of FEMBurgers, by name without the suffix) for every
+    (mu1[b], mu2[b]) and write one .npy per sample in the reference's format and naming, so that POD/pod.py:80-82
+    and the other offline stages consume GPU-generated data unchanged.
+    Extra keyword arguments (Phi=..., projection=..., H=...) go to the trajectory method.
+    Returns (paths, iters) with iters a (B, nTimeSteps) int32 numpy array."""
+    import os
+    from concurrent.futures import ThreadPoolExecutor
+    os.makedirs(directory, exist_ok=True)
+    mu1 = np.asarray(mu1, dtype=np.float64).reshape(-1)
+    mu2 = np.asarray(mu2, dtype=np.float64).reshape(-1)
+    B, N, nT = mu1.size, fem.n_nodes, int(nTimeSteps)
+    if mu2.size != B:
+        raise ValueError("mu1 and mu2 must have the same number of samples")
+    run = getattr(fem, method + "_batch")
+    chunk = max(1, min(int(chunk), max(B, 1)))
+    dev = fem.device
+    dU = torch.empty((chunk, nT + 1, N), dtype=torch.float64, device=dev)
+    dIt = [torch.empty((chunk, nT), dtype=torch.int32, device=dev) for _ in range(2)]
+    dUr = [torch.empty((chunk, N, nT + 1), dtype=torch.float64, device=dev) for _ in range(2)]
+    hUr = [torch.empty((chunk, N, nT + 1), dtype=torch.float64).pin_memory() for _ in range(2)]
+    hIt = [torch.empty((chunk, nT), dtype=torch.int32).pin_memory() for _ in range(2)]
+    copy_stream = torch.cuda.Stream(device=dev)
+    compute = torch.cuda.current_stream()
+    iters = np.empty((B, nT), dtype=np.int32)
+    paths = [os.path.join(directory, name(float(a), float(b))) for a, b in zip(mu1, mu2)]
+    copied = [None, None]
+    pending = [None, None]
+    futures = [[], []]
+    u0d = fem._dev(u0)
+
+    with ThreadPoolExecutor(max_workers=max(1, int(writers))) as pool:
+        def drain(i):
+            if pending[i] is None:
+                return
+            copied[i].synchronize()
+            lo, hi = pending[i]
+            iters[lo:hi] = hIt[i][: hi - lo].numpy()
+            view = hUr[i].numpy()
+            futures[i] = [pool.submit(_write_npy, paths[lo + k], view[k]) for k in range(hi - lo)]
+            pending[i] = None
+
+        def wait_writes(i):
+            for f in futures[i]:
+                f.result()
+            futures[i] = []
+
+        for c, lo in enumerate(range(0, B, chunk)):
+            hi = min(B, lo + chunk)
+            n = hi - lo
+            i = c & 1
+            drain(1 - i)       # hand the previous chunk to the writers while this one integrates
+            wait_writes(i)     # host buffer i is about to be overwritten
+            a = torch.from_numpy(mu1[lo:hi]).to(dev, non_blocking=True)
+            b = torch.from_numpy(mu2[lo:hi]).to(dev, non_blocking=True)
+            if copied[i] is not None:
+                compute.wait_event(copied[i])   # dUr[i] / dIt[i] still being copied out
+            u0c = u0d if u0d.numel() == N else u0d.reshape(B, N)[lo:hi]
+            run(At, nT, u0c, a, E, b, out=dU[:n], iters_out=dIt[i][:n], **kwargs)
+            to_reference_layout(fem, dU[:n], out=dUr[i][:n])
+            done = torch.cuda.Event()
+            done.record(compute)
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(done)
+                hUr[i][:n].copy_(dUr[i][:n], non_blocking=True)
+                hIt[i][:n].copy_(dIt[i][:n], non_blocking=True)
+                copied[i] = torch.cuda.Event()
+                copied[i].record(copy_stream)
+            pending[i] = (lo, hi)
+        drain(0); drain(1)
+        wait_writes(0); wait_writes(1)
+    return paths, iters
 
 
 class HostSweepBuffers:

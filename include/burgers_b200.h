@@ -153,6 +153,13 @@ long long bx_gram_workspace_bytes(int N, long long cols);
 int bx_gram_accumulate(int N, long long cols, const double *S, double *G, int accumulate,
                        void *workspace, void *stream);
 
+/* ---- on-disk snapshot format of the sweep drivers (FEM/paper_training_stage.py:52-53) ------------------ */
+/* Trajectory buffer U (B, rows, N) (one snapshot per row, as the trajectory entry points write it) ->
+ * Uref (B, N, rows): per sample the array FEMBurgers.fom_burgers returns, (N, nTimeSteps+1) C order
+ * (FEM/fem_burgers.py:650, 705), i.e. the payload of one `fem_simulation_mu1_*_mu2_*.npy` file that
+ * POD/pod.py:80-82 loads and hstacks.  Batched tiled transpose; U and Uref must not alias; B <= 65535.   */
+int bx_snapshots_to_reference_layout(int B, int rows, int N, const double *U, double *Uref, void *stream);
+
 #ifdef __cplusplus
 }
 #endif
