@@ -9,5 +9,6 @@ from .build import build_library, LIB_PATH  # noqa: F401
 from .fem_burgers import FEMBurgers, validate_mesh  # noqa: F401
 from . import sweep  # noqa: F401
 from . import pod  # noqa: F401
+from . import quadratic  # noqa: F401
 
 __all__ = ["FEMBurgers", "validate_mesh", "build_library", "LIB_PATH", "BurgersB200Error"]

@@ -2,7 +2,7 @@
 
 Run in the build container only (needs /root/reference):
     python tests/golden/make_golden.py [section ...]
-Sections: ops fom_short newton_short prom_short qm_short fom_fixtures prom_fixtures qm_fixtures pod
+Sections: ops fom_short newton_short prom_short qm_short fom_fixtures prom_fixtures qm_fixtures pod qm_build
 `fom_fixtures` additionally needs the full 500-step reference runs produced by
 make_ref_full_fom.py (per-step iteration counts parsed from the reference's stdout); point
 BURGERS_REF_FULL at the directory holding fom_<mu1>_<mu2>.npz (default /tmp/reffull).
@@ -220,6 +220,19 @@ def sec_pod():
     out["stored_counts"] = np.array([load_phi(t).shape[1] for t in
                                      ("1e-02", "4e-03", "3e-03", "1e-03", "1e-04", "1e-05", "1e-06")])
     np.savez_compressed(os.path.join(HERE, "pod.npz"), **out)
+
+
+def sec_qm_build():
+    """Quadratic_manifold/quad_utils.py run on a small seeded case (the builder's three functions)."""
+    sys.path.insert(0, os.path.join(REF_ROOT, "Quadratic_manifold"))
+    import quad_utils as qu
+    rng = np.random.default_rng(5)
+    n, Ns, N = 5, 60, 14
+    q = rng.standard_normal((n, Ns)); S = rng.standard_normal((N, Ns))
+    Phi = np.linalg.qr(rng.standard_normal((N, n)))[0]
+    Q = qu.build_Q(q); E = qu.build_E(S, Phi, Phi.T @ S, None)
+    H = qu.compute_H(qu.build_Q(Phi.T @ S), E, 1e-2)
+    np.savez(os.path.join(HERE, "qm_build.npz"), q=q, S=S, Phi=Phi, Q=Q, E=E, H=H, alpha=1e-2)
 
 
 SECTIONS = {k[4:]: v for k, v in list(globals().items()) if k.startswith("sec_")}

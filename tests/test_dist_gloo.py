@@ -74,3 +74,49 @@ def test_shard_range_covers_everything():
             assert all(edges[i][1] == edges[i + 1][0] for i in range(w - 1))
             sizes = [b - a for a, b in edges]
             assert max(sizes) - min(sizes) <= 1
+
+
+def _qm_worker(rank, world, port, out):
+    """Quadratic-manifold builder across ranks: each rank reduces its own snapshot columns to (R, W) — here with
+    numpy (test infrastructure; on a GPU box burgers_b200.quadratic.reduce_snapshots does it on the device) — and the
+    product's exchange step (all-gather + ordered merge) and compute_H_from_factors run on the gloo group."""
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    import burgers_b200  # noqa: F401
+    from burgers_b200 import quadratic, sweep
+    from oracle import burgers_oracle as O
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    rng = np.random.default_rng(7)
+    N, n, Ns = 24, 4, 90
+    S = rng.standard_normal((N, Ns)); Phi = np.linalg.qr(rng.standard_normal((N, n)))[0]
+    lo, hi = sweep.shard_range(Ns, rank, world)
+    Sl = S[:, lo:hi]
+    q = Phi.T @ Sl
+    Q1, R = np.linalg.qr(O.build_Q(q).T)
+    W = Q1.T @ O.build_E(Sl, Phi, q).T
+    Rm, Wm = quadratic.merge_across_ranks(torch.from_numpy(R), torch.from_numpy(W))
+    H = quadratic.compute_H_from_factors(Rm, Wm, 1e-2)
+    np.savez(out, H=H.numpy(), S=S, Phi=Phi)
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_quadratic_builder_exchange_step(tmp_path, oracle):
+    import torch.multiprocessing as mp
+    world, port = 2, _free_port()
+    outs = [str(tmp_path / f"q{r}.npz") for r in range(world)]
+    ctx = mp.get_context("spawn")
+    procs = [ctx.Process(target=_qm_worker, args=(r, world, port, outs[r])) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(240)
+        assert p.exitcode == 0
+    r0, r1 = np.load(outs[0]), np.load(outs[1])
+    assert np.array_equal(r0["H"], r1["H"])          # identical on every rank, no broadcast
+    S, Phi = r0["S"], r0["Phi"]
+    q = Phi.T @ S
+    H = oracle.compute_H(oracle.build_Q(q), oracle.build_E(S, Phi, q), 1e-2)
+    assert np.linalg.norm(r0["H"] - H) <= 1e-11 * np.linalg.norm(H)
