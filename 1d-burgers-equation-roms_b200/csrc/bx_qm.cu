@@ -9,10 +9,17 @@
 //     u_i = (Phi_i + T_i) . q / 2     (q^T Hs_i q / 2 = sum_{a<=b} H[i][ab] q_a q_b)
 // so each Gauss-Newton iteration makes one pass over H (k = n(n+1)/2 doubles per node).
 //
-// One WARP integrates one trajectory (up to 8 per CTA, no CTA-wide barrier in the time loop):
-//   T  tangent/decoder pass: four nodes at a time, their packed H rows staged in shared memory,
-//      lane j owns column j; T rows go to a per-warp scratch in global memory (L2 resident), u to
-//      shared memory.
+// A CTA integrates EIGHT trajectories in lock step (one warp owns one trajectory for the contraction and the
+// reduced solve; the tangent pass is shared):
+//   T  tangent/decoder pass on the FP64 tensor pipe: for node i the eight tangent rows are the 8 x n product
+//      [q_0 .. q_7]^T Hs_i, i.e. DMMA m8n8k4 with A = Hs_i (rows j, k index m, streamed ONCE per CTA from an
+//      L2-resident unpacked copy laid out in fragment order: 64 contiguous bytes per lane and 8-row block),
+//      B = the eight q vectors, C initialised with Phi_i.  Warp w takes nodes w, w + 8, ...; the next node's
+//      fragments are in flight while the current one is multiplied.  u_i = (Phi_i + T_i) . q / 2 comes from the
+//      same accumulators (reduction over the 8 row lanes).  T rows go to per-trajectory scratch in global
+//      memory (L2), u to the owning warp's shared memory.  Trajectories that have converged keep taking part
+//      with an unchanged q (the pass reproduces their T and u bit for bit) until all eight are done with the
+//      time step (__syncthreads_and).
 //   B  contraction on the FP64 tensor pipe (DMMA m8n8k4, k index = node) exactly as in bx_prom.cu with
 //      T in the place of Phi and no SUPG term in b (:1141):
 //         LSPG  Ar = (A T)^T (A T), br = (A T)^T R (:1153-1156);  Galerkin  Ar = T^T A T, br = T^T R (:1150-1151)
@@ -33,7 +40,7 @@ struct QmParams {
     const double *mu2;
     double At, E, tol;
     const double *Phi;   // (N, n) row-major
-    const double *Hp;    // workspace: (NP4, k) H with doubled diagonal monomials, zero rows beyond N
+    const double *Hs;    // workspace: (N, NB, 32 lanes, 2 NB) unpacked symmetric H rows in DMMA A-fragment order
     double *atf;         // workspace: At * F (B, N)
     double *Tg;          // workspace: per warp slot (NP + 1) x 32 tangent rows (row 0 = zero row for node -1)
     double *U;
@@ -42,12 +49,11 @@ struct QmParams {
 };
 
 constexpr int QM_MAXW = 8;
-constexpr int QM_NODES = 4;   // nodes per tangent step
 
 struct QmSmem {
     int h6, per_cta;
-    int u, misc, bn, hrow, per_warp, arr;
-    __host__ __device__ static QmSmem make(int NP, int k) {
+    int u, misc, bn, per_warp, arr;
+    __host__ __device__ static QmSmem make(int NP) {
         QmSmem m;
         m.arr = NP + 8;
         int o = 0;
@@ -59,25 +65,34 @@ struct QmSmem {
         m.u = o; o += usz;
         m.misc = o; o += 128;
         m.bn = o; o += m.arr;
-        o = (o + 1) & ~1;
-        m.hrow = o; o += (QM_NODES * k + 1) & ~1;
         m.per_warp = (o + 1) & ~1;
         return m;
     }
 };
 
-// Hp[i][c] = H[i][c] * (2 if monomial c is a square q_a^2 else 1); rows N .. NP4-1 are zero.  atf = At F.
-__global__ void __launch_bounds__(256) qm_prep_kernel(int B, int N, int NP4, int n, int k, const double *X,
-                                                      const double *mu2v, double At, const double *H, double *Hp,
+// Hs: for node i, 8-row block jb, lane (g = lane / 4, t = lane % 4), k-step ks the entry
+//   Hs_i[j = 8 jb + g][m = 4 ks + t] = H[i][idx(min(j, m), max(j, m))] (1 + delta_jm)   (0 beyond n),
+// stored at ((i NB + jb) 32 + lane) 2 NB + ks — the A fragments of one (node, block) are 64-byte runs per lane.
+// atf = At F.
+__global__ void __launch_bounds__(256) qm_prep_kernel(int B, int N, int NB, int n, int k, const double *X,
+                                                      const double *mu2v, double At, const double *H, double *Hs,
                                                       double *atf) {
     const long long idx = (long long)blockIdx.x * 256 + threadIdx.x;
-    const long long nH = (long long)NP4 * k;
+    const int NKS = 2 * NB;
+    const long long nH = (long long)N * NB * 32 * NKS;
     if (idx < nH) {
-        const int i = (int)(idx / k), c = (int)(idx - (long long)i * k);
-        // c is a diagonal monomial iff c = a n - a (a - 1) / 2 for some a
-        int a = 0, base = 0;
-        while (base + (n - a) <= c) { base += n - a; ++a; }
-        Hp[idx] = (i < N) ? H[(size_t)i * k + c] * (c == base ? 2.0 : 1.0) : 0.0;
+        const int ks = (int)(idx % NKS);
+        long long r = idx / NKS;
+        const int lane = (int)(r & 31); r >>= 5;
+        const int jb = (int)(r % NB), i = (int)(r / NB);
+        const int j = 8 * jb + (lane >> 2), m = 4 * ks + (lane & 3);
+        double v = 0.0;
+        if (j < n && m < n) {
+            const int a = j < m ? j : m, b = j < m ? m : j;
+            const int c = a * n - a * (a - 1) / 2 + (b - a);
+            v = H[(size_t)i * k + c] * (a == b ? 2.0 : 1.0);
+        }
+        Hs[idx] = v;
         return;
     }
     const long long j = idx - nH;
@@ -107,11 +122,10 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel(const QmParams p) {
     constexpr int TILES = Tl::COUNT;
     extern __shared__ __align__(16) double smem[];
 
-    const int N = p.N, n = p.n, kq = p.k;
+    const int N = p.N, n = p.n;
     const PromGeom geo = PromGeom::make(N);
     const int S = geo.S, lgS = geo.lgS, NP = geo.NP;
-    const int NP4 = (N + QM_NODES - 1) / QM_NODES * QM_NODES;
-    const QmSmem lay = QmSmem::make(NP, kq);
+    const QmSmem lay = QmSmem::make(NP);
     double *s_h6 = smem + lay.h6;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -120,12 +134,13 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel(const QmParams p) {
     double *w_u = wbase + lay.u;
     double *w_misc = wbase + lay.misc;
     double *w_bn = wbase + lay.bn;
-    double *w_h = wbase + lay.hrow;
     double *w_mat = w_u;                 // 16 x MAT_LD, over the dead u (+ the first words of misc)
     double *w_piv = w_misc + 16;         // pivot rows, 2 x (NC+2) (<= 68)
     double *w_q = w_misc + 96;           // q (32), zero beyond n
     // tangent rows of this warp: row r = node r - 1, r = 0 .. NP + 1 (rows 0 and > N stay zero)
-    double *Tw = p.Tg + ((size_t)blockIdx.x * p.warps + warp) * (size_t)(NP + 2) * 32;
+    const size_t tstride = (size_t)(NP + 2) * 32;
+    double *Tcta = p.Tg + (size_t)blockIdx.x * QM_MAXW * tstride;
+    double *Tw = Tcta + warp * tstride;
 
     const double At = p.At;
 
@@ -147,67 +162,88 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel(const QmParams p) {
     rc.a6 = At / 6.0; rc.c1 = 0.0; rc.ate = At * p.E; rc.has_e = p.E != 0.0; rc.supg = false;
     rc.N = N; rc.S = S; rc.lgS = lgS;
 
-    // column owned by this lane in the tangent pass; lanes >= n shadow column n-1 and discard
-    const int jc = lane < n ? lane : n - 1;
+    const int jc = lane < n ? lane : n - 1;   // column of Phi^T U this lane owns (lanes >= n shadow n - 1 and discard)
 
-    // tangent/decoder pass at the q published in w_q: T rows -> Tw, u -> w_u
-    auto tangent_pass = [&]() {
-        const double qj = lane < n ? w_q[lane] : 0.0;
-        for (int i0 = 0; i0 < NP4; i0 += QM_NODES) {
-            {
-                const double2 *src = reinterpret_cast<const double2 *>(p.Hp + (size_t)i0 * kq);
-                double2 *dst = reinterpret_cast<double2 *>(w_h);
-                for (int x = lane; x < (QM_NODES / 2) * kq; x += 32) dst[x] = src[x];
-            }
-            __syncwarp();
-            double phi[QM_NODES], acc[QM_NODES];
+    // ---- tangent / decoder pass for the eight trajectories of the CTA at the q's published in the w_q's ----
+    constexpr int NKS = 2 * NB;
+    auto load_A = [&](double (&A)[NB][NKS], int i) {
+        const double2 *src = reinterpret_cast<const double2 *>(p.Hs + ((size_t)i * NB * 32 + lane) * NKS);
 #pragma unroll
-            for (int r = 0; r < QM_NODES; ++r) {
-                phi[r] = (lane < n && i0 + r < N) ? p.Phi[(size_t)(i0 + r) * n + lane] : 0.0;
-                acc[r] = phi[r];
-            }
-            int idx = jc;
-            for (int m = 0; m < n; ++m) {
-                const double qm = w_q[m];
+        for (int jb = 0; jb < NB; ++jb) {
 #pragma unroll
-                for (int r = 0; r < QM_NODES; ++r) acc[r] = fma(w_h[r * kq + idx], qm, acc[r]);
-                idx += (m < jc) ? (n - m - 1) : 1;
+            for (int h = 0; h < NB; ++h) {
+                const double2 v = src[(size_t)jb * 32 * NB + h];
+                A[jb][2 * h] = v.x; A[jb][2 * h + 1] = v.y;
             }
-            double part[QM_NODES];
-#pragma unroll
-            for (int r = 0; r < QM_NODES; ++r) {
-                const double tv = lane < n ? acc[r] : 0.0;
-                Tw[(size_t)(i0 + r + 1) * 32 + lane] = tv;
-                part[r] = (phi[r] + tv) * qj;
-            }
-            // sum the four node values over the warp: recursive halving, then a butterfly
-            double w2[2];
-#pragma unroll
-            for (int j = 0; j < 2; ++j) {
-                const double send = (lane & 16) ? part[j] : part[j + 2];
-                const double keep = (lane & 16) ? part[j + 2] : part[j];
-                w2[j] = keep + shfl_xor(send, 16);
-            }
-            double v;
-            {
-                const double send = (lane & 8) ? w2[0] : w2[1];
-                const double keep = (lane & 8) ? w2[1] : w2[0];
-                v = keep + shfl_xor(send, 8);
-            }
-            v += shfl_xor(v, 4);
-            v += shfl_xor(v, 2);
-            v += shfl_xor(v, 1);
-            const int node = i0 + ((lane >> 3) & 3);
-            if ((lane & 7) == 0 && node < N) w_u[sk(node, S, lgS)] = 0.5 * v;
-            __syncwarp();
         }
     };
+    auto tangent_pass = [&]() {
+        __syncthreads();   // every q published; nobody still reads T / u of the previous pass
+        double Bq[NKS], qC[NB][2];
+        {
+            const double *qg = smem + lay.per_cta + g * lay.per_warp + lay.misc + 96;         // q of trajectory g
+            const double *q0 = smem + lay.per_cta + (2 * t) * lay.per_warp + lay.misc + 96;   // trajectories 2t, 2t+1
+            const double *q1 = q0 + lay.per_warp;
+#pragma unroll
+            for (int ks = 0; ks < NKS; ++ks) Bq[ks] = qg[4 * ks + t];
+#pragma unroll
+            for (int jb = 0; jb < NB; ++jb) { qC[jb][0] = q0[8 * jb + g]; qC[jb][1] = q1[8 * jb + g]; }
+        }
+        double *u0s = smem + lay.per_cta + (2 * t) * lay.per_warp + lay.u;   // u of trajectory 2t (2t+1: + per_warp)
+        auto node = [&](const double (&A)[NB][NKS], int i) {
+            double c[NB][2], ph[NB];
+#pragma unroll
+            for (int jb = 0; jb < NB; ++jb) {
+                ph[jb] = (8 * jb + g < n) ? p.Phi[(size_t)i * n + 8 * jb + g] : 0.0;
+                c[jb][0] = ph[jb]; c[jb][1] = ph[jb];
+            }
+#pragma unroll
+            for (int ks = 0; ks < NKS; ++ks) {
+#pragma unroll
+                for (int jb = 0; jb < NB; ++jb) dmma884(c[jb][0], c[jb][1], A[jb][ks], Bq[ks]);
+            }
+            double s0 = 0.0, s1 = 0.0;
+            double *T0 = Tcta + (size_t)(2 * t) * tstride + (size_t)(i + 1) * 32 + g;
+#pragma unroll
+            for (int jb = 0; jb < NB; ++jb) {
+                T0[8 * jb] = c[jb][0];
+                T0[tstride + 8 * jb] = c[jb][1];
+                s0 = fma(ph[jb] + c[jb][0], qC[jb][0], s0);
+                s1 = fma(ph[jb] + c[jb][1], qC[jb][1], s1);
+            }
+            s0 += shfl_xor(s0, 4); s1 += shfl_xor(s1, 4);
+            s0 += shfl_xor(s0, 8); s1 += shfl_xor(s1, 8);
+            s0 += shfl_xor(s0, 16); s1 += shfl_xor(s1, 16);
+            if (g == 0) {
+                const int o = sk(i, S, lgS);
+                u0s[o] = 0.5 * s0;
+                u0s[lay.per_warp + o] = 0.5 * s1;
+            }
+        };
+        double A0[NB][NKS], A1[NB][NKS];
+        int i = warp;
+        if (i < N) load_A(A0, i);
+        while (i < N) {
+            const int i1 = i + QM_MAXW;
+            if (i1 < N) load_A(A1, i1);
+            node(A0, i);
+            if (i1 >= N) break;
+            const int i2 = i1 + QM_MAXW;
+            if (i2 < N) load_A(A0, i2);
+            node(A1, i1);
+            i = i2;
+        }
+        __syncthreads();   // T rows (global) and u (shared) of all trajectories written
+    };
 
+    __shared__ int s_base;
     for (;;) {
-        int smp = 0;
-        if (lane == 0) smp = (int)atomicAdd(p.counter, 1u);
-        smp = __shfl_sync(FULL, smp, 0);
-        if (smp >= p.B) break;
+        __syncthreads();
+        if (threadIdx.x == 0) s_base = (int)atomicAdd(p.counter, (unsigned)QM_MAXW);
+        __syncthreads();
+        if (s_base >= p.B) break;
+        const bool active = s_base + warp < p.B;          // a ragged last group runs idle warps (q = 0)
+        const int smp = active ? s_base + warp : p.B - 1;
         rc.mu1 = p.mu1[smp];
         const double *atf = p.atf + (size_t)smp * N;
 
@@ -216,10 +252,10 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel(const QmParams p) {
             const double *u0p = p.u0 + (long long)smp * p.u0_stride;
             for (int i = lane - 1; i <= NP; i += 32) {
                 const int o = sk(i, S, lgS);
-                const double v = (i >= 0 && i < N) ? u0p[i] : 0.0;
+                const double v = (active && i >= 0 && i < N) ? u0p[i] : 0.0;
                 w_u[o] = v;
                 w_bn[o] = 0.0;
-                if (i >= 0 && i < N) Us[i] = v;
+                if (active && i >= 0 && i < N) Us[i] = v;
             }
         }
         __syncwarp();
@@ -241,15 +277,16 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel(const QmParams p) {
                     for (int r = 0; r < 4; ++r) q4[r] = fma(ph[(size_t)(i + r) * n], w_u[sk(i + r, S, lgS)], q4[r]);
                 }
                 for (; i < N; ++i) q4[0] = fma(ph[(size_t)i * n], w_u[sk(i, S, lgS)], q4[0]);
-                q = lane < n ? (q4[0] + q4[1]) + (q4[2] + q4[3]) : 0.0;
+                q = (active && lane < n) ? (q4[0] + q4[1]) + (q4[2] + q4[3]) : 0.0;
             }
             __syncwarp();
             w_q[lane] = q;
-            __syncwarp();
             tangent_pass();   // u = decoder(q) (:1130), T(q)
 
             int it_done = 0;
+            bool done = !active;
             for (int it = 0; it < p.itmax; ++it) {
+              if (!done) {
                 // ================= contraction (:1134-1156) ==================================
                 double acc[TILES][2];
 #pragma unroll
@@ -330,22 +367,24 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel(const QmParams p) {
                 w_q[lane] = q;
                 if (lane == 0) { w_u[sk(-1, S, lgS)] = 0.0; w_u[sk(NP, S, lgS)] = 0.0; }   // halo words the matrix overwrote
                 for (int i = N + lane; i < NP; i += 32) w_u[sk(i, S, lgS)] = 0.0;           // padded nodes likewise
-                __syncwarp();
-                tangent_pass();   // u = decoder(q) (:1163) and the tangent of the next iteration
                 it_done = it + 1;
-                if (rel < p.tol) break;
+                if (rel < p.tol) done = true;
+              }
+                tangent_pass();   // u = decoder(q) (:1163) and the tangent of the next iteration
+                if (__syncthreads_and(done ? 1 : 0)) break;
             }
-            double *Un1 = Us + (long long)(step + 1) * N;
-            for (int i = lane; i < N; i += 32) Un1[i] = w_u[sk(i, S, lgS)];
-            if (lane == 0 && p.iters) p.iters[(long long)smp * p.nsteps + step] = it_done;
+            if (active) {
+                double *Un1 = Us + (long long)(step + 1) * N;
+                for (int i = lane; i < N; i += 32) Un1[i] = w_u[sk(i, S, lgS)];
+                if (lane == 0 && p.iters) p.iters[(long long)smp * p.nsteps + step] = it_done;
+            }
         }
-        __syncwarp();
     }
 }
 
 struct QmPlan {
-    int sms, NP, NP4;
-    size_t off_hp, off_atf, off_tg, total;
+    int sms, NP, NB;
+    size_t off_hs, off_atf, off_tg, total;
 };
 
 static int qm_plan(int B, int N, int n, QmPlan &pl) {
@@ -354,10 +393,9 @@ static int qm_plan(int B, int N, int n, QmPlan &pl) {
     BX_CUDA(cudaDeviceGetAttribute(&pl.sms, cudaDevAttrMultiProcessorCount, dev));
     const PromGeom geo = PromGeom::make(N);
     pl.NP = geo.NP;
-    pl.NP4 = (N + QM_NODES - 1) / QM_NODES * QM_NODES;
-    const size_t k = (size_t)n * (n + 1) / 2;
+    pl.NB = n / 8 + 1;   // 8 NB > n: column n of the contraction carries R
     size_t o = 256;
-    pl.off_hp = o; o += sizeof(double) * (size_t)pl.NP4 * k; o = (o + 255) & ~(size_t)255;
+    pl.off_hs = o; o += sizeof(double) * (size_t)N * pl.NB * 32 * 2 * pl.NB; o = (o + 255) & ~(size_t)255;
     pl.off_atf = o; o += sizeof(double) * (size_t)B * N; o = (o + 255) & ~(size_t)255;
     pl.off_tg = o; o += sizeof(double) * (size_t)pl.sms * QM_MAXW * (size_t)(pl.NP + 2) * 32;
     pl.total = o;
@@ -366,18 +404,15 @@ static int qm_plan(int B, int N, int n, QmPlan &pl) {
 
 template <int NB, bool LSPG>
 static int launch_qm_t(QmParams p, const QmPlan &pl, const double *H, cudaStream_t st) {
-    const QmSmem lay = QmSmem::make(pl.NP, p.k);
+    const QmSmem lay = QmSmem::make(pl.NP);
     int dev = 0, maxsm = 0;
     BX_CUDA(cudaGetDevice(&dev));
     BX_CUDA(cudaDeviceGetAttribute(&maxsm, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
-    const long long avail = (long long)maxsm / (long long)sizeof(double) - lay.per_cta;
-    long long warps = avail > 0 ? avail / lay.per_warp : 0;
-    if (warps > QM_MAXW) warps = QM_MAXW;
-    if (warps < 1) {
+    const long long warps = QM_MAXW;   // eight trajectories per CTA in lock step (the M of the tangent DMMA)
+    if ((long long)sizeof(double) * (lay.per_cta + warps * lay.per_warp) > (long long)maxsm) {
         set_error("bx_qm_prom_trajectories: N = %d, n = %d does not fit in shared memory", p.N, p.n);
         return BX_ERR_UNSUPPORTED;
     }
-    if (warps > p.B) warps = p.B;
     p.warps = (int)warps;
     const size_t smem = sizeof(double) * ((size_t)lay.per_cta + (size_t)warps * lay.per_warp);
     auto kern = qm_kernel<NB, LSPG>;
@@ -386,9 +421,9 @@ static int launch_qm_t(QmParams p, const QmPlan &pl, const double *H, cudaStream
     const long long need = ((long long)p.B + warps - 1) / warps;
     if (ctas > need) ctas = need;
     BX_CUDA(cudaMemsetAsync(p.counter, 0, sizeof(unsigned int), st));
-    const long long work = (long long)pl.NP4 * p.k + (long long)p.B * p.N;
-    qm_prep_kernel<<<(unsigned)((work + 255) / 256), 256, 0, st>>>(p.B, p.N, pl.NP4, p.n, p.k, p.X, p.mu2, p.At, H,
-                                                                 const_cast<double *>(p.Hp), p.atf);
+    const long long work = (long long)p.N * NB * 32 * 2 * NB + (long long)p.B * p.N;
+    qm_prep_kernel<<<(unsigned)((work + 255) / 256), 256, 0, st>>>(p.B, p.N, NB, p.n, p.k, p.X, p.mu2, p.At, H,
+                                                                 const_cast<double *>(p.Hs), p.atf);
     BX_LAUNCH_CHECK();
     kern<<<(unsigned)ctas, (unsigned)warps * 32, smem, st>>>(p);
     BX_LAUNCH_CHECK();
@@ -441,7 +476,7 @@ extern "C" int bx_qm_prom_trajectories(int B, int N, int n, int nsteps, const do
     p.mu1 = uxa; p.mu2 = mu2; p.At = At; p.E = E; p.tol = tol;
     p.Phi = Phi;
     p.counter = reinterpret_cast<unsigned int *>(ws);
-    p.Hp = reinterpret_cast<double *>(ws + pl.off_hp);
+    p.Hs = reinterpret_cast<double *>(ws + pl.off_hs);
     p.atf = reinterpret_cast<double *>(ws + pl.off_atf);
     p.Tg = reinterpret_cast<double *>(ws + pl.off_tg);
     p.U = U; p.iters = iters;
