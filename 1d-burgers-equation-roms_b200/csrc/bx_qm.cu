@@ -49,6 +49,7 @@ struct QmParams {
 };
 
 constexpr int QM_MAXW = 8;
+constexpr int QM_PF = 4;      // tangent rows in flight ahead of the contraction (divides 8)
 
 struct QmSmem {
     int h6, per_cta;
@@ -138,7 +139,7 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel(const QmParams p) {
     double *w_piv = w_misc + 16;         // pivot rows, 2 x (NC+2) (<= 68)
     double *w_q = w_misc + 96;           // q (32), zero beyond n
     // tangent rows of this warp: row r = node r - 1, r = 0 .. NP + 1 (rows 0 and > N stay zero)
-    const size_t tstride = (size_t)(NP + 2) * 32;
+    const size_t tstride = (size_t)(NP + 2 + QM_PF) * 32;
     double *Tcta = p.Tg + (size_t)blockIdx.x * QM_MAXW * tstride;
     double *Tw = Tcta + warp * tstride;
 
@@ -147,7 +148,7 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel(const QmParams p) {
     for (int idx = threadIdx.x; idx < lay.arr; idx += blockDim.x) s_h6[idx] = 0.0;
     __syncthreads();
     for (int e = threadIdx.x; e <= N - 2; e += blockDim.x) s_h6[sk(e, S, lgS)] = (p.X[e + 1] - p.X[e]) / 6.0;
-    for (int r = lane; r < (NP + 2) * 32; r += 32)
+    for (int r = lane; r < (NP + 2 + QM_PF) * 32; r += 32)
         if (r < 32 || r >= (N + 1) * 32) Tw[r] = 0.0;
     __syncthreads();
 
@@ -292,10 +293,15 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel(const QmParams p) {
 #pragma unroll
                 for (int i = 0; i < TILES; ++i) { acc[i][0] = 0.0; acc[i][1] = 0.0; }
                 double pm[NB], p0[NB], pp[NB];
+                // tangent rows come from L2 / HBM (written by the tangent pass of all eight warps): a four-deep
+                // register ring keeps the loads QM_PF node steps ahead of the DMMAs that consume them
+                double ring[QM_PF][NB];
 #pragma unroll
                 for (int b = 0; b < NB; ++b) {
                     pm[b] = t_run[-32 + b * 8 + g];
                     p0[b] = t_run[b * 8 + g];
+#pragma unroll
+                    for (int r = 0; r < QM_PF; ++r) ring[r][b] = t_run[(r + 1) * 32 + b * 8 + g];
                 }
                 PromRow nxt = prom_row(rc, run0 + g, ubase + g);
                 for (int blk = 0; blk < nblk; ++blk) {
@@ -304,9 +310,12 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel(const QmParams p) {
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
                         const int s = (blk << 3) + j;
-                        const double *rp = t_run + (size_t)(s + 1) * 32;
+                        const double *rp = t_run + (size_t)(s + 1 + QM_PF) * 32;   // (rows past the run end: padding)
 #pragma unroll
-                        for (int b = 0; b < NB; ++b) pp[b] = rp[b * 8 + g];
+                        for (int b = 0; b < NB; ++b) {
+                            pp[b] = ring[j % QM_PF][b];
+                            ring[j % QM_PF][b] = rp[b * 8 + g];
+                        }
                         const int src = 4 * j + t;
                         const double ra = shfl_idx(cur.a, src), rb = shfl_idx(cur.b, src);
                         const double rcc = shfl_idx(cur.c, src), rR = shfl_idx(cur.R, src);
@@ -397,7 +406,7 @@ static int qm_plan(int B, int N, int n, QmPlan &pl) {
     size_t o = 256;
     pl.off_hs = o; o += sizeof(double) * (size_t)N * pl.NB * 32 * 2 * pl.NB; o = (o + 255) & ~(size_t)255;
     pl.off_atf = o; o += sizeof(double) * (size_t)B * N; o = (o + 255) & ~(size_t)255;
-    pl.off_tg = o; o += sizeof(double) * (size_t)pl.sms * QM_MAXW * (size_t)(pl.NP + 2) * 32;
+    pl.off_tg = o; o += sizeof(double) * (size_t)pl.sms * QM_MAXW * (size_t)(pl.NP + 2 + QM_PF) * 32;
     pl.total = o;
     return BX_OK;
 }
