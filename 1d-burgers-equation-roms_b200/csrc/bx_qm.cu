@@ -391,6 +391,348 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel(const QmParams p) {
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// v3: same lock-step design, but the tangent rows never leave the SM.  The nodes are cut into chunks that follow
+// the contraction's own order (its four k-lanes walk four runs of S nodes in parallel): chunk blk holds, for
+// run t and j = 0..7, the tangent row of node t S + 8 blk + j + 1 — exactly the rows block blk of the contraction
+// consumes as its "next node" operand.  Per barrier interval every warp first multiplies its four nodes of chunk
+// blk + 1 (DMMA, Hs fragments from L2) into one half of a double-buffered shared tile [8 trajectories][32 nodes]
+// [32 columns] (XOR-swizzled: conflict-free for the fragment stores and for the contraction's loads), then runs
+// block blk of its own trajectory's contraction out of the other half.  The seven run-boundary rows a contraction
+// starts from go through the small global scratch (prologue).  A final tangent-only pass per time step leaves
+// u = decoder(q) of every trajectory in shared memory (:1163).
+struct QmTsSmem {
+    int T, total;
+    __host__ __device__ static int trajstride() { return 32 * 32 + 2; }   // 2 mod 16: fragment stores conflict-free
+    __host__ __device__ static QmTsSmem make(const QmSmem &lay) {
+        QmTsSmem m;
+        int o = lay.per_cta + QM_MAXW * lay.per_warp;
+        o = (o + 1) & ~1;
+        m.T = o; o += 2 * QM_MAXW * trajstride();
+        m.total = o;
+        return m;
+    }
+};
+
+template <int NB, bool LSPG>
+__global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel_ts(const QmParams p) {
+    constexpr int NC = NB * 8;
+    constexpr int NKS = 2 * NB;
+    using Tl = PromTiles<NB, LSPG>;
+    constexpr int TILES = Tl::COUNT;
+    extern __shared__ __align__(16) double smem[];
+
+    const int N = p.N, n = p.n;
+    const PromGeom geo = PromGeom::make(N);
+    const int S = geo.S, lgS = geo.lgS, NP = geo.NP;
+    const QmSmem lay = QmSmem::make(NP);
+    const QmTsSmem tl = QmTsSmem::make(lay);
+    constexpr int TSTR = 32 * 32 + 2;
+    double *s_h6 = smem + lay.h6;
+    double *s_T = smem + tl.T;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int t = lane & 3, g = lane >> 2;
+    double *wbase = smem + lay.per_cta + warp * lay.per_warp;
+    double *w_u = wbase + lay.u;
+    double *w_misc = wbase + lay.misc;
+    double *w_bn = wbase + lay.bn;
+    double *w_mat = w_u;
+    double *w_piv = w_misc + 16;
+    double *w_q = w_misc + 96;
+    // global scratch: only the run-boundary rows are used (row r = node r - 1; rows 0 and > N stay zero)
+    const size_t tstride = (size_t)(NP + 2 + QM_PF) * 32;
+    double *Tcta = p.Tg + (size_t)blockIdx.x * QM_MAXW * tstride;
+    double *Tw = Tcta + warp * tstride;
+
+    const double At = p.At;
+    for (int idx = threadIdx.x; idx < lay.arr; idx += blockDim.x) s_h6[idx] = 0.0;
+    __syncthreads();
+    for (int e = threadIdx.x; e <= N - 2; e += blockDim.x) s_h6[sk(e, S, lgS)] = (p.X[e + 1] - p.X[e]) / 6.0;
+    for (int r = lane; r < (NP + 2 + QM_PF) * 32; r += 32)
+        if (r < 32 || r >= (N + 1) * 32) Tw[r] = 0.0;
+    __syncthreads();
+
+    const int run0 = t << lgS;
+    const int ubase = t * (S + 1) + 2;
+    const int gR = n & 7;
+    const int nblk = S >> 3;
+    const double *t_run = Tw + (size_t)(run0 + 1) * 32;
+    // this warp's trajectory inside a shared T buffer: row of (j, t) at (4 j + t) 32, column c at c ^ 4 t
+    const int myT = warp * TSTR + t * 32;
+
+    PromRowCtx rc;
+    rc.u = w_u; rc.bn = w_bn; rc.hfs = nullptr; rc.h6 = s_h6;
+    rc.a6 = At / 6.0; rc.c1 = 0.0; rc.ate = At * p.E; rc.has_e = p.E != 0.0; rc.supg = false;
+    rc.N = N; rc.S = S; rc.lgS = lgS;
+    const int jc = lane < n ? lane : n - 1;
+
+    // q fragments of the eight trajectories (owners' shared memory), loaded once per chunk
+    const double *qB = smem + lay.per_cta + g * lay.per_warp + lay.misc + 96 + t;            // B operand: q of trajectory g
+    const double *qC0 = smem + lay.per_cta + (2 * t) * lay.per_warp + lay.misc + 96 + g;     // trajectories 2t, 2t+1
+    auto load_q = [&](double (&Bq)[NKS], double (&qC)[NB][2]) {
+#pragma unroll
+        for (int ks = 0; ks < NKS; ++ks) Bq[ks] = qB[4 * ks];
+#pragma unroll
+        for (int jb = 0; jb < NB; ++jb) { qC[jb][0] = qC0[8 * jb]; qC[jb][1] = qC0[lay.per_warp + 8 * jb]; }
+    };
+    auto load_A = [&](double (&A)[NB][NKS], int i) {
+        const double2 *src = reinterpret_cast<const double2 *>(p.Hs + ((size_t)i * NB * 32 + lane) * NKS);
+#pragma unroll
+        for (int jb = 0; jb < NB; ++jb) {
+#pragma unroll
+            for (int h = 0; h < NB; ++h) {
+                const double2 v = src[(size_t)jb * 32 * NB + h];
+                A[jb][2 * h] = v.x; A[jb][2 * h + 1] = v.y;
+            }
+        }
+    };
+    double *u0s = smem + lay.per_cta + (2 * t) * lay.per_warp + lay.u;
+    // eight tangent rows + eight u values of node i; dstS != nullptr: rows to the shared tile (row base dstS of
+    // trajectory 0, swizzle sw), else to the global scratch.  While the DMMAs of k-steps 2h, 2h+1 retire, the
+    // registers they read are refilled with the same fragments of node `inext` (>= 0): one buffer, a full node of
+    // prefetch distance.
+    auto node = [&](double (&A)[NB][NKS], const double (&Bq)[NKS], const double (&qC)[NB][2], int i, int inext,
+                    double *dstS, int sw) {
+        double c[NB][2], ph[NB];
+#pragma unroll
+        for (int jb = 0; jb < NB; ++jb) {
+            ph[jb] = (8 * jb + g < n) ? p.Phi[(size_t)i * n + 8 * jb + g] : 0.0;
+            c[jb][0] = ph[jb]; c[jb][1] = ph[jb];
+        }
+        const double2 *nsrc = reinterpret_cast<const double2 *>(p.Hs + ((size_t)(inext < 0 ? 0 : inext) * NB * 32 + lane) * NKS);
+#pragma unroll
+        for (int h = 0; h < NB; ++h) {
+#pragma unroll
+#pragma unroll
+            for (int jb = 0; jb < NB; ++jb) dmma884(c[jb][0], c[jb][1], A[jb][2 * h], Bq[2 * h]);
+#pragma unroll
+            for (int jb = 0; jb < NB; ++jb) dmma884(c[jb][0], c[jb][1], A[jb][2 * h + 1], Bq[2 * h + 1]);
+            if (inext >= 0) {
+#pragma unroll
+                for (int jb = 0; jb < NB; ++jb) {
+                    const double2 v = nsrc[(size_t)jb * 32 * NB + h];
+                    A[jb][2 * h] = v.x; A[jb][2 * h + 1] = v.y;
+                }
+            }
+        }
+        double s0 = 0.0, s1 = 0.0;
+        if (dstS) {
+            double *T0 = dstS + (2 * t) * TSTR;
+#pragma unroll
+            for (int jb = 0; jb < NB; ++jb) {
+                T0[(8 * jb + g) ^ sw] = c[jb][0];
+                T0[TSTR + ((8 * jb + g) ^ sw)] = c[jb][1];
+            }
+        } else {
+            double *T0 = Tcta + (size_t)(2 * t) * tstride + (size_t)(i + 1) * 32 + g;
+#pragma unroll
+            for (int jb = 0; jb < NB; ++jb) { T0[8 * jb] = c[jb][0]; T0[tstride + 8 * jb] = c[jb][1]; }
+        }
+#pragma unroll
+        for (int jb = 0; jb < NB; ++jb) {
+            s0 = fma(ph[jb] + c[jb][0], qC[jb][0], s0);
+            s1 = fma(ph[jb] + c[jb][1], qC[jb][1], s1);
+        }
+        s0 += shfl_xor(s0, 4); s1 += shfl_xor(s1, 4);
+        s0 += shfl_xor(s0, 8); s1 += shfl_xor(s1, 8);
+        s0 += shfl_xor(s0, 16); s1 += shfl_xor(s1, 16);
+        if (g == 0) {
+            const int o = sk(i, S, lgS);
+            u0s[o] = 0.5 * s0;
+            u0s[lay.per_warp + o] = 0.5 * s1;
+        }
+    };
+    // tangent rows of chunk blk into shared buffer `buf`: this warp takes rows nidx = warp, warp + 8, +16, +24
+    // (node index grows with r, so the rows past N form a tail)
+    auto chunk_pass = [&](int blk, int buf) {
+        double *base = s_T + buf * (QM_MAXW * TSTR);
+        double A[NB][NKS], Bq[NKS], qC[NB][2];
+        load_q(Bq, qC);
+        auto nd = [&](int r) { const int nidx = warp + 8 * r; return ((nidx & 3) << lgS) + (blk << 3) + (nidx >> 2) + 1; };
+        bool have = false;
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const int nidx = warp + 8 * r, i = nd(r);
+            if (i < N) {
+                if (!have) load_A(A, i);
+                const int inx = r < 3 ? nd(r + 1) : N;
+                have = inx < N;
+                node(A, Bq, qC, i, have ? inx : -1, base + nidx * 32, 4 * (nidx & 3));
+            } else {
+                have = false;
+                double *d = base + nidx * 32 + lane;   // all 32 columns (the swizzle permutes within a row)
+#pragma unroll
+                for (int tr = 0; tr < QM_MAXW; ++tr) d[tr * TSTR] = 0.0;
+            }
+        }
+    };
+
+    __shared__ int s_base;
+    for (;;) {
+        __syncthreads();
+        if (threadIdx.x == 0) s_base = (int)atomicAdd(p.counter, (unsigned)QM_MAXW);
+        __syncthreads();
+        if (s_base >= p.B) break;
+        const bool active = s_base + warp < p.B;
+        const int smp = active ? s_base + warp : p.B - 1;
+        rc.mu1 = p.mu1[smp];
+        const double *atf = p.atf + (size_t)smp * N;
+        double *Us = p.U + (long long)smp * (long long)(p.nsteps + 1) * N;
+        {
+            const double *u0p = p.u0 + (long long)smp * p.u0_stride;
+            for (int i = lane - 1; i <= NP; i += 32) {
+                const int o = sk(i, S, lgS);
+                const double v = (active && i >= 0 && i < N) ? u0p[i] : 0.0;
+                w_u[o] = v;
+                w_bn[o] = 0.0;
+                if (active && i >= 0 && i < N) Us[i] = v;
+            }
+        }
+        __syncwarp();
+
+        for (int step = 0; step < p.nsteps; ++step) {
+            for (int i = lane; i < N; i += 32) {
+                const double h6L = s_h6[sk(i - 1, S, lgS)], h6R = s_h6[sk(i, S, lgS)];
+                const double um = w_u[sk(i - 1, S, lgS)], uc = w_u[sk(i, S, lgS)], up = w_u[sk(i + 1, S, lgS)];
+                w_bn[sk(i, S, lgS)] = h6L * um + (2.0 * (h6L + h6R)) * uc + h6R * up + atf[i];
+            }
+            double q;
+            {
+                double q4[4] = {0.0, 0.0, 0.0, 0.0};
+                const double *ph = p.Phi + jc;
+                int i = 0;
+                for (; i + 4 <= N; i += 4) {
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) q4[r] = fma(ph[(size_t)(i + r) * n], w_u[sk(i + r, S, lgS)], q4[r]);
+                }
+                for (; i < N; ++i) q4[0] = fma(ph[(size_t)i * n], w_u[sk(i, S, lgS)], q4[0]);
+                q = (active && lane < n) ? (q4[0] + q4[1]) + (q4[2] + q4[3]) : 0.0;
+            }
+            __syncwarp();
+            w_q[lane] = q;
+
+            int it_done = 0;
+            bool done = !active;
+            for (int it = 0; it < p.itmax; ++it) {
+                // ---- prologue: run-boundary rows (global scratch) and chunk 0 ----------------------------
+                __syncthreads();   // every q published; previous contraction / solve finished
+                if (warp < 7) {
+                    const int tb = (warp + 1) >> 1;                       // 0, 1, 1, 2, 2, 3, 3
+                    const int i = warp == 0 ? 0 : (tb << lgS) - (warp & 1);   // 0, S-1, S, 2S-1, 2S, 3S-1, 3S
+                    if (i < N) {
+                        double Ab[NB][NKS], Bq[NKS], qC[NB][2];
+                        load_q(Bq, qC);
+                        load_A(Ab, i);
+                        node(Ab, Bq, qC, i, -1, nullptr, 0);
+                    }
+                }
+                chunk_pass(0, 0);
+                __syncthreads();
+                double acc[TILES][2];
+#pragma unroll
+                for (int i = 0; i < TILES; ++i) { acc[i][0] = 0.0; acc[i][1] = 0.0; }
+                double pm[NB], p0[NB], pp[NB];
+#pragma unroll
+                for (int b = 0; b < NB; ++b) {
+                    pm[b] = t_run[-32 + b * 8 + g];
+                    p0[b] = t_run[b * 8 + g];
+                }
+                for (int blk = 0; blk < nblk; ++blk) {
+                    if (blk + 1 < nblk) chunk_pass(blk + 1, (blk + 1) & 1);
+                    if (!done) {
+                        const PromRow cur = prom_row(rc, run0 + (blk << 3) + g, ubase + (blk << 3) + g);
+                        const double *Tb = s_T + (blk & 1) * (QM_MAXW * TSTR) + myT;
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+#pragma unroll
+                            for (int b = 0; b < NB; ++b) pp[b] = Tb[j * 128 + ((b * 8 + g) ^ (4 * t))];
+                            const int src = 4 * j + t;
+                            const double ra = shfl_idx(cur.a, src), rb = shfl_idx(cur.b, src);
+                            const double rcc = shfl_idx(cur.c, src), rR = shfl_idx(cur.R, src);
+                            double jp[NB];
+#pragma unroll
+                            for (int b = 0; b < NB; ++b) jp[b] = fma(ra, pm[b], fma(rb, p0[b], rcc * pp[b]));
+                            if (g == gR) jp[NB - 1] = rR;
+#pragma unroll
+                            for (int I = 0; I < NB; ++I) {
+#pragma unroll
+                                for (int J = LSPG ? I : 0; J < NB; ++J) {
+                                    const int ti = Tl::index(I, J);
+                                    dmma884(acc[ti][0], acc[ti][1], LSPG ? jp[I] : p0[I], jp[J]);
+                                }
+                            }
+#pragma unroll
+                            for (int b = 0; b < NB; ++b) { pm[b] = p0[b]; p0[b] = pp[b]; }
+                        }
+                    }
+                    __syncthreads();
+                }
+                if (!done) {
+                    // ================= reduced solve (:1161-1165) ===============================
+                    double a[NC];
+                    double rhs = 0.0;
+#pragma unroll
+                    for (int pass = 0; pass < (NB + 1) / 2; ++pass) {
+                        __syncwarp();
+#pragma unroll
+                        for (int I = 0; I < NB; ++I) {
+#pragma unroll
+                            for (int J = LSPG ? I : 0; J < NB; ++J) {
+                                const int ti = Tl::index(I, J);
+                                const int r = I * 8 + g, c = J * 8 + 2 * t;
+                                if ((I >> 1) == pass) {
+                                    w_mat[(r - 16 * pass) * MAT_LD + c] = acc[ti][0];
+                                    w_mat[(r - 16 * pass) * MAT_LD + c + 1] = acc[ti][1];
+                                }
+                                if (LSPG && J > I && (J >> 1) == pass) {
+                                    w_mat[(c - 16 * pass) * MAT_LD + r] = acc[ti][0];
+                                    w_mat[(c + 1 - 16 * pass) * MAT_LD + r] = acc[ti][1];
+                                }
+                            }
+                        }
+                        __syncwarp();
+                        if (pass == 0 || lane >= 16) {
+                            const double *mr = w_mat + (lane & 15) * MAT_LD;
+#pragma unroll
+                            for (int j = 0; j < NC; ++j) a[j] = mr[j];
+                            rhs = -mr[n];
+                        }
+                    }
+                    __syncwarp();
+                    const double dq = lu_solve_rows<NC, true>(a, rhs, n, lane, w_piv);
+                    q = (lane < n) ? q + dq : 0.0;
+                    const double sd = warp_sum((lane < n) ? dq * dq : 0.0);
+                    const double sq = warp_sum(q * q);
+                    const double rel = sqrt(sd) / fmax(1e-14, sqrt(sq));
+                    __syncwarp();
+                    w_q[lane] = q;
+                    if (lane == 0) { w_u[sk(-1, S, lgS)] = 0.0; w_u[sk(NP, S, lgS)] = 0.0; }
+                    for (int i = N + lane; i < NP; i += 32) w_u[sk(i, S, lgS)] = 0.0;
+                    it_done = it + 1;
+                    if (rel < p.tol) done = true;
+                }
+                if (__syncthreads_and(done ? 1 : 0)) break;
+            }
+            // ---- u = decoder(q) at the final q of every trajectory (:1163 / :1130): tangent-only pass -----
+            __syncthreads();
+            for (int blk = 0; blk < nblk; ++blk) chunk_pass(blk, 0);
+            if (warp == 0) {   // node 0 is in no chunk (chunks hold rows 8 blk + j + 1)
+                double Ab[NB][NKS], Bq[NKS], qC[NB][2];
+                load_q(Bq, qC);
+                load_A(Ab, 0);
+                node(Ab, Bq, qC, 0, -1, nullptr, 0);
+            }
+            __syncthreads();
+            if (active) {
+                double *Un1 = Us + (long long)(step + 1) * N;
+                for (int i = lane; i < N; i += 32) Un1[i] = w_u[sk(i, S, lgS)];
+                if (lane == 0 && p.iters) p.iters[(long long)smp * p.nsteps + step] = it_done;
+            }
+        }
+    }
+}
+
 struct QmPlan {
     int sms, NP, NB;
     size_t off_hs, off_atf, off_tg, total;
@@ -423,8 +765,15 @@ static int launch_qm_t(QmParams p, const QmPlan &pl, const double *H, cudaStream
         return BX_ERR_UNSUPPORTED;
     }
     p.warps = (int)warps;
-    const size_t smem = sizeof(double) * ((size_t)lay.per_cta + (size_t)warps * lay.per_warp);
+    size_t smem = sizeof(double) * ((size_t)lay.per_cta + (size_t)warps * lay.per_warp);
     auto kern = qm_kernel<NB, LSPG>;
+    const QmTsSmem tl = QmTsSmem::make(lay);
+    // tangent rows in shared memory (v3) where the register budget allows it: with n >= 24 (NB = 4) the 32 accumulators
+    // of the contraction and the tangent fragments spill, and the version with the global scratch is faster (measured)
+    if (NB <= 3 && sizeof(double) * (size_t)tl.total <= (size_t)maxsm) {
+        kern = qm_kernel_ts<NB, LSPG>;
+        smem = sizeof(double) * (size_t)tl.total;
+    }
     BX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     long long ctas = pl.sms;
     const long long need = ((long long)p.B + warps - 1) / warps;
