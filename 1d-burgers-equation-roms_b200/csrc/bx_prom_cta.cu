@@ -23,6 +23,7 @@
 // HBM traffic: the 8N-byte snapshot per time step; Phi is re-read from L2 twice per iteration.
 #include "bx_prom_common.cuh"
 #include "bx_async.cuh"
+#include <cstdlib>
 
 namespace bx {
 
@@ -524,35 +525,50 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
     p.ldp = p.NC + 4;                 // 4 mod 8: conflict-free DMMA fragment loads
     p.ldm = (n + 1) | 1;              // odd, >= n + 1
     p.units = projection == BX_LSPG ? p.NBu * (p.NBu + 1) / 2 : p.NBu * p.NBu;
-    int W = 8;   // at least 8 warps: staging, the J pass and the lift are per-warp instruction bound
-    while (W < PC_MAXW && (W * PC_UB < p.units || W * 32 < p.NC)) W *= 2;
-    p.passes = (p.units + W * PC_UB - 1) / (W * PC_UB);
+    // Launch shape: W warps per trajectory and KC nodes per chunk chosen to keep the most warps resident per SM
+    // (shared memory per CTA; 128 registers per thread = 512 threads per SM); ties go to the smaller CTA (more
+    // trajectories in different phases per SM), then to the larger chunk (fewer barriers).  Measured on B200
+    // (profiles/r02d_prom_cta_tune.txt): n = 40 -> (8, 16), n = 64 -> (8, 8), n = 96 -> (16, 16).
+    int Wmin = 8;   // at least 8 warps: staging, the J pass and the lift are per-warp instruction bound
+    while (Wmin < PC_MAXW && (Wmin * PC_UB < p.units || Wmin * 32 < p.NC)) Wmin *= 2;
+    int force_w = 0, force_kc = 0;
+    if (const char *e = getenv("BX_PROM_CTA_TUNE")) {   // tuning aid: "W,KC" (e.g. 16,32); invalid values are ignored
+        int w = 0, kc = 0;
+        if (sscanf(e, "%d,%d", &w, &kc) == 2) {
+            if ((w == 8 || w == 16) && w >= Wmin) force_w = w;
+            if (kc == 8 || kc == 16 || kc == 32) force_kc = kc;
+        }
+    }
     p.lgS = 3;
     while ((1 << p.lgS) < N) ++p.lgS;
     int dev = 0, sms = 0, maxsm = 0;
     BX_CUDA(cudaGetDevice(&dev));
     BX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     BX_CUDA(cudaDeviceGetAttribute(&maxsm, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
-    // chunk size: the one that keeps the most warps resident (2048 threads, 228 KB per SM), larger chunks on a
-    // tie; reduced system in shared memory if it fits at all
     static const int kcs[3] = {32, 16, 8};
     PromCtaSmem lay;
     bool found = false;
-    for (int mg = 0; mg < 2 && !found; ++mg) {
-        int best_occ = 0, best_kc = 0;
-        for (int ki = 0; ki < 3; ++ki) {
-            const int kc = kcs[ki];
-            const int nch = (N + kc - 1) / kc;
-            const PromCtaSmem l = PromCtaSmem::make(N, n, p.NC, p.ldp, p.ldm, kc, nch * kc, p.lgS, W, mg ? 0 : 1);
-            const long long bytes = (long long)l.total * (long long)sizeof(double);
-            if (bytes > (long long)maxsm) continue;
-            int o = (int)(233472LL / (bytes + 1024));
-            if (o > 2048 / (W * 32)) o = 2048 / (W * 32);
-            if (o > 4) o = 4;
-            if (o > best_occ) { best_occ = o; best_kc = kc; }
+    int W = Wmin;
+    for (int mg = 0; mg < 2 && !found; ++mg) {   // reduced system in shared memory if it fits at all
+        int best_score = 0, best_kc = 0, best_w = 0;
+        for (int w = Wmin; w <= PC_MAXW; w *= 2) {
+            if (force_w && w != force_w) continue;
+            for (int ki = 0; ki < 3; ++ki) {
+                const int kc = kcs[ki];
+                if (force_kc && kc != force_kc) continue;
+                const int nch = (N + kc - 1) / kc;
+                const PromCtaSmem l = PromCtaSmem::make(N, n, p.NC, p.ldp, p.ldm, kc, nch * kc, p.lgS, w, mg ? 0 : 1);
+                const long long bytes = (long long)l.total * (long long)sizeof(double);
+                if (bytes > (long long)maxsm) continue;
+                int o = (int)(233472LL / (bytes + 1024));
+                if (o > 512 / (w * 32)) o = 512 / (w * 32);
+                if (o < 1) o = 1;
+                if (o * w > best_score) { best_score = o * w; best_kc = kc; best_w = w; }
+            }
         }
-        if (best_occ > 0) {
+        if (best_score > 0) {
             found = true;
+            W = best_w;
             p.KC = best_kc;
             p.nchunks = (N + p.KC - 1) / p.KC;
             p.NPad = p.nchunks * p.KC;
@@ -560,6 +576,7 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
             lay = PromCtaSmem::make(N, n, p.NC, p.ldp, p.ldm, p.KC, p.NPad, p.lgS, W, mg ? 0 : 1);
         }
     }
+    p.passes = (p.units + W * PC_UB - 1) / (W * PC_UB);
     if (found) {
         p.CG = 1;
         while (p.CG * 32 < p.NC) p.CG *= 2;

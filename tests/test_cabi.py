@@ -71,3 +71,23 @@ def test_no_cpu_fallback():
     fem = burgers_b200.FEMBurgers(np.linspace(0, 100, 64))
     with pytest.raises(RuntimeError):
         fem.fom_burgers(0.05, 2, np.ones(64), 4.75, 0.0, 0.02)
+
+
+def test_reference_file_names_and_npy_writer(tmp_path):
+    """Host logic of the on-disk side (no GPU): the reference's file names (FEM/paper_training_stage.py:52,
+    POD/Results_thesis/prom_pod.py:59-60 — names of files the reference ships) and the header + raw-bytes writer."""
+    from burgers_b200 import sweep
+    assert sweep.snapshot_filename(4.25, 0.015) == "fem_simulation_mu1_4.250_mu2_0.0150.npy"
+    assert sweep.snapshot_filename(4.875, 0.0225) == "fem_simulation_mu1_4.875_mu2_0.0225.npy"
+    assert sweep.snapshot_filename(6.2, 0.04) == "fem_simulation_mu1_6.200_mu2_0.0400.npy"
+    assert sweep.prom_filename(1e-3, 4.75, 0.02, "LSPG") == "U_PROM_tol_1e-03_mu1_4.750_mu2_0.0200_lspg.npy"
+    assert sweep.prom_filename(4e-3, 5.19, 0.026, "Galerkin") == "U_PROM_tol_4e-03_mu1_5.190_mu2_0.0260_galerkin.npy"
+    mu1, mu2 = sweep.parameter_grid(3, 3)      # mu1-major, as [[a, b] for a in mu1 for b in mu2]
+    assert list(mu1[:4]) == [4.25, 4.25, 4.25, 4.875] and list(mu2[:4]) == [0.015, 0.0225, 0.03, 0.015]
+    a = np.arange(512 * 7, dtype=np.float64).reshape(512, 7) / 3.0
+    sweep._write_npy(str(tmp_path / "a.npy"), a)
+    b = np.load(tmp_path / "a.npy")
+    assert b.dtype == np.float64 and b.shape == (512, 7) and np.array_equal(a, b)
+    it = np.arange(12, dtype=np.int32).reshape(3, 4)
+    sweep._write_npy(str(tmp_path / "it.npy"), it)
+    assert np.array_equal(np.load(tmp_path / "it.npy"), it)
