@@ -28,6 +28,7 @@
 // A pre-kernel doubles the diagonal monomials of H once (Hp) and evaluates At F per sample.
 #include "bx_prom_common.cuh"
 #include <cstdint>
+#include <cstdlib>
 
 namespace bx {
 
@@ -49,6 +50,7 @@ struct QmParams {
 };
 
 constexpr int QM_MAXW = 8;
+constexpr int QM_TS_MAX_NB = 3;   // v3 is dispatched up to this many 8-column blocks (n <= 23)
 constexpr int QM_PF = 4;      // tangent rows in flight ahead of the contraction (divides 8)
 
 struct QmSmem {
@@ -116,6 +118,73 @@ __global__ void __launch_bounds__(256) qm_prep_kernel(int B, int N, int NB, int 
     atf[j] = At * F;
 }
 
+// ---- tangent pass building block shared by qm_kernel (v2) and qm_kernel_ts (v3) ---------------------------
+// A node is multiplied in two halves of HB = ceil(NB / 2) eight-row blocks: 16 instead of 32 fragment doubles
+// live per lane, which is what lets the tangent pass coexist with the 32 accumulators of an NB = 4 contraction.
+// qm_half: eight tangent half-rows T_i[8 jb + g], jb in [hh HB, hh HB + HB), of the trajectories 2t, 2t+1 (c0 / c1),
+// C initialised with Phi_i; while the DMMAs of k-steps 2h, 2h+1 retire, the fragment registers they read are
+// refilled with those of the next half (node inext, half hnext; inext < 0: none) — one buffer, a whole half
+// of prefetch distance.  s0 / s1 accumulate the decoder partial sums (Phi_i + T_i) . q of the two trajectories.
+template <int NB>
+__device__ __forceinline__ void qm_load_half(double (&A)[(NB + 1) / 2][2 * NB], const double *Hs, int lane, int i, int hh) {
+    constexpr int HB = (NB + 1) / 2, NKS = 2 * NB;
+#pragma unroll
+    for (int b = 0; b < HB; ++b) {
+        const int jb = hh * HB + b;
+        if (jb < NB) {
+            const double2 *src = reinterpret_cast<const double2 *>(Hs + (((size_t)i * NB + jb) * 32 + lane) * NKS);
+#pragma unroll
+            for (int h = 0; h < NB; ++h) {
+                const double2 v = src[h];
+                A[b][2 * h] = v.x; A[b][2 * h + 1] = v.y;
+            }
+        }
+    }
+}
+
+template <int NB>
+__device__ __forceinline__ void qm_half(double (&A)[(NB + 1) / 2][2 * NB], const double (&Bq)[2 * NB],
+                                        const double (&qC)[NB][2], const double *Hs, const double *Phi, int n, int lane,
+                                        int i, int hh, int inext, int hnext, double (&c)[(NB + 1) / 2][2],
+                                        double &s0, double &s1) {
+    constexpr int HB = (NB + 1) / 2, NKS = 2 * NB;
+    const int g = lane >> 2;
+    double ph[HB];
+#pragma unroll
+    for (int b = 0; b < HB; ++b) {
+        const int jb = hh * HB + b;
+        ph[b] = (jb < NB && 8 * jb + g < n) ? Phi[(size_t)i * n + 8 * jb + g] : 0.0;
+        c[b][0] = ph[b]; c[b][1] = ph[b];
+    }
+#pragma unroll
+    for (int h = 0; h < NB; ++h) {
+#pragma unroll
+        for (int b = 0; b < HB; ++b)
+            if (hh * HB + b < NB) dmma884(c[b][0], c[b][1], A[b][2 * h], Bq[2 * h]);
+#pragma unroll
+        for (int b = 0; b < HB; ++b)
+            if (hh * HB + b < NB) dmma884(c[b][0], c[b][1], A[b][2 * h + 1], Bq[2 * h + 1]);
+        if (inext >= 0) {
+#pragma unroll
+            for (int b = 0; b < HB; ++b) {
+                const int jn = hnext * HB + b;
+                if (jn < NB) {
+                    const double2 v = reinterpret_cast<const double2 *>(Hs + (((size_t)inext * NB + jn) * 32 + lane) * NKS)[h];
+                    A[b][2 * h] = v.x; A[b][2 * h + 1] = v.y;
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int b = 0; b < HB; ++b) {
+        const int jb = hh * HB + b;
+        if (jb < NB) {
+            s0 = fma(ph[b] + c[b][0], (hh ? qC[HB + b < NB ? HB + b : 0][0] : qC[b][0]), s0);
+            s1 = fma(ph[b] + c[b][1], (hh ? qC[HB + b < NB ? HB + b : 0][1] : qC[b][1]), s1);
+        }
+    }
+}
+
 template <int NB, bool LSPG>
 __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel(const QmParams p) {
     constexpr int NC = NB * 8;
@@ -167,17 +236,7 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel(const QmParams p) {
 
     // ---- tangent / decoder pass for the eight trajectories of the CTA at the q's published in the w_q's ----
     constexpr int NKS = 2 * NB;
-    auto load_A = [&](double (&A)[NB][NKS], int i) {
-        const double2 *src = reinterpret_cast<const double2 *>(p.Hs + ((size_t)i * NB * 32 + lane) * NKS);
-#pragma unroll
-        for (int jb = 0; jb < NB; ++jb) {
-#pragma unroll
-            for (int h = 0; h < NB; ++h) {
-                const double2 v = src[(size_t)jb * 32 * NB + h];
-                A[jb][2 * h] = v.x; A[jb][2 * h + 1] = v.y;
-            }
-        }
-    };
+    constexpr int HB = (NB + 1) / 2;
     auto tangent_pass = [&]() {
         __syncthreads();   // every q published; nobody still reads T / u of the previous pass
         double Bq[NKS], qC[NB][2];
@@ -191,26 +250,21 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel(const QmParams p) {
             for (int jb = 0; jb < NB; ++jb) { qC[jb][0] = q0[8 * jb + g]; qC[jb][1] = q1[8 * jb + g]; }
         }
         double *u0s = smem + lay.per_cta + (2 * t) * lay.per_warp + lay.u;   // u of trajectory 2t (2t+1: + per_warp)
-        auto node = [&](const double (&A)[NB][NKS], int i) {
-            double c[NB][2], ph[NB];
-#pragma unroll
-            for (int jb = 0; jb < NB; ++jb) {
-                ph[jb] = (8 * jb + g < n) ? p.Phi[(size_t)i * n + 8 * jb + g] : 0.0;
-                c[jb][0] = ph[jb]; c[jb][1] = ph[jb];
-            }
-#pragma unroll
-            for (int ks = 0; ks < NKS; ++ks) {
-#pragma unroll
-                for (int jb = 0; jb < NB; ++jb) dmma884(c[jb][0], c[jb][1], A[jb][ks], Bq[ks]);
-            }
+        double A[HB][NKS];
+        if (warp < N) qm_load_half<NB>(A, p.Hs, lane, warp, 0);
+        for (int i = warp; i < N; i += QM_MAXW) {
             double s0 = 0.0, s1 = 0.0;
             double *T0 = Tcta + (size_t)(2 * t) * tstride + (size_t)(i + 1) * 32 + g;
 #pragma unroll
-            for (int jb = 0; jb < NB; ++jb) {
-                T0[8 * jb] = c[jb][0];
-                T0[tstride + 8 * jb] = c[jb][1];
-                s0 = fma(ph[jb] + c[jb][0], qC[jb][0], s0);
-                s1 = fma(ph[jb] + c[jb][1], qC[jb][1], s1);
+            for (int hh = 0; hh < 2; ++hh) {
+                double c[HB][2];
+                const int inext = hh == 0 ? i : (i + QM_MAXW < N ? i + QM_MAXW : -1);
+                qm_half<NB>(A, Bq, qC, p.Hs, p.Phi, n, lane, i, hh, inext, 1 - hh, c, s0, s1);
+#pragma unroll
+                for (int b2 = 0; b2 < HB; ++b2) {
+                    const int jb = hh * HB + b2;
+                    if (jb < NB) { T0[8 * jb] = c[b2][0]; T0[tstride + 8 * jb] = c[b2][1]; }
+                }
             }
             s0 += shfl_xor(s0, 4); s1 += shfl_xor(s1, 4);
             s0 += shfl_xor(s0, 8); s1 += shfl_xor(s1, 8);
@@ -220,19 +274,6 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel(const QmParams p) {
                 u0s[o] = 0.5 * s0;
                 u0s[lay.per_warp + o] = 0.5 * s1;
             }
-        };
-        double A0[NB][NKS], A1[NB][NKS];
-        int i = warp;
-        if (i < N) load_A(A0, i);
-        while (i < N) {
-            const int i1 = i + QM_MAXW;
-            if (i1 < N) load_A(A1, i1);
-            node(A0, i);
-            if (i1 >= N) break;
-            const int i2 = i1 + QM_MAXW;
-            if (i2 < N) load_A(A0, i2);
-            node(A1, i1);
-            i = i2;
         }
         __syncthreads();   // T rows (global) and u (shared) of all trajectories written
     };
@@ -476,63 +517,33 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel_ts(const QmParams p
 #pragma unroll
         for (int jb = 0; jb < NB; ++jb) { qC[jb][0] = qC0[8 * jb]; qC[jb][1] = qC0[lay.per_warp + 8 * jb]; }
     };
-    auto load_A = [&](double (&A)[NB][NKS], int i) {
-        const double2 *src = reinterpret_cast<const double2 *>(p.Hs + ((size_t)i * NB * 32 + lane) * NKS);
-#pragma unroll
-        for (int jb = 0; jb < NB; ++jb) {
-#pragma unroll
-            for (int h = 0; h < NB; ++h) {
-                const double2 v = src[(size_t)jb * 32 * NB + h];
-                A[jb][2 * h] = v.x; A[jb][2 * h + 1] = v.y;
-            }
-        }
-    };
+    constexpr int HB = (NB + 1) / 2;
     double *u0s = smem + lay.per_cta + (2 * t) * lay.per_warp + lay.u;
-    // eight tangent rows + eight u values of node i; dstS != nullptr: rows to the shared tile (row base dstS of
-    // trajectory 0, swizzle sw), else to the global scratch.  While the DMMAs of k-steps 2h, 2h+1 retire, the
-    // registers they read are refilled with the same fragments of node `inext` (>= 0): one buffer, a full node of
-    // prefetch distance.
-    auto node = [&](double (&A)[NB][NKS], const double (&Bq)[NKS], const double (&qC)[NB][2], int i, int inext,
+    // one node for the eight trajectories (two halves); dstS != nullptr: rows to the shared tile (row base dstS of
+    // trajectory 0, swizzle sw), else to the global scratch.  A holds half 0 of node i on entry and half 0 of node
+    // inext (if >= 0) on exit.
+    auto node = [&](double (&A)[HB][NKS], const double (&Bq)[NKS], const double (&qC)[NB][2], int i, int inext,
                     double *dstS, int sw) {
-        double c[NB][2], ph[NB];
+        double s0 = 0.0, s1 = 0.0;
 #pragma unroll
-        for (int jb = 0; jb < NB; ++jb) {
-            ph[jb] = (8 * jb + g < n) ? p.Phi[(size_t)i * n + 8 * jb + g] : 0.0;
-            c[jb][0] = ph[jb]; c[jb][1] = ph[jb];
-        }
-        const double2 *nsrc = reinterpret_cast<const double2 *>(p.Hs + ((size_t)(inext < 0 ? 0 : inext) * NB * 32 + lane) * NKS);
+        for (int hh = 0; hh < 2; ++hh) {
+            double c[HB][2];
+            qm_half<NB>(A, Bq, qC, p.Hs, p.Phi, n, lane, i, hh, hh == 0 ? i : inext, 1 - hh, c, s0, s1);
+            if (dstS) {
+                double *T0 = dstS + (2 * t) * TSTR;
 #pragma unroll
-        for (int h = 0; h < NB; ++h) {
+                for (int b2 = 0; b2 < HB; ++b2) {
+                    const int jb = hh * HB + b2;
+                    if (jb < NB) { T0[(8 * jb + g) ^ sw] = c[b2][0]; T0[TSTR + ((8 * jb + g) ^ sw)] = c[b2][1]; }
+                }
+            } else {
+                double *T0 = Tcta + (size_t)(2 * t) * tstride + (size_t)(i + 1) * 32 + g;
 #pragma unroll
-#pragma unroll
-            for (int jb = 0; jb < NB; ++jb) dmma884(c[jb][0], c[jb][1], A[jb][2 * h], Bq[2 * h]);
-#pragma unroll
-            for (int jb = 0; jb < NB; ++jb) dmma884(c[jb][0], c[jb][1], A[jb][2 * h + 1], Bq[2 * h + 1]);
-            if (inext >= 0) {
-#pragma unroll
-                for (int jb = 0; jb < NB; ++jb) {
-                    const double2 v = nsrc[(size_t)jb * 32 * NB + h];
-                    A[jb][2 * h] = v.x; A[jb][2 * h + 1] = v.y;
+                for (int b2 = 0; b2 < HB; ++b2) {
+                    const int jb = hh * HB + b2;
+                    if (jb < NB) { T0[8 * jb] = c[b2][0]; T0[tstride + 8 * jb] = c[b2][1]; }
                 }
             }
-        }
-        double s0 = 0.0, s1 = 0.0;
-        if (dstS) {
-            double *T0 = dstS + (2 * t) * TSTR;
-#pragma unroll
-            for (int jb = 0; jb < NB; ++jb) {
-                T0[(8 * jb + g) ^ sw] = c[jb][0];
-                T0[TSTR + ((8 * jb + g) ^ sw)] = c[jb][1];
-            }
-        } else {
-            double *T0 = Tcta + (size_t)(2 * t) * tstride + (size_t)(i + 1) * 32 + g;
-#pragma unroll
-            for (int jb = 0; jb < NB; ++jb) { T0[8 * jb] = c[jb][0]; T0[tstride + 8 * jb] = c[jb][1]; }
-        }
-#pragma unroll
-        for (int jb = 0; jb < NB; ++jb) {
-            s0 = fma(ph[jb] + c[jb][0], qC[jb][0], s0);
-            s1 = fma(ph[jb] + c[jb][1], qC[jb][1], s1);
         }
         s0 += shfl_xor(s0, 4); s1 += shfl_xor(s1, 4);
         s0 += shfl_xor(s0, 8); s1 += shfl_xor(s1, 8);
@@ -547,7 +558,7 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel_ts(const QmParams p
     // (node index grows with r, so the rows past N form a tail)
     auto chunk_pass = [&](int blk, int buf) {
         double *base = s_T + buf * (QM_MAXW * TSTR);
-        double A[NB][NKS], Bq[NKS], qC[NB][2];
+        double A[HB][NKS], Bq[NKS], qC[NB][2];
         load_q(Bq, qC);
         auto nd = [&](int r) { const int nidx = warp + 8 * r; return ((nidx & 3) << lgS) + (blk << 3) + (nidx >> 2) + 1; };
         bool have = false;
@@ -555,7 +566,7 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel_ts(const QmParams p
         for (int r = 0; r < 4; ++r) {
             const int nidx = warp + 8 * r, i = nd(r);
             if (i < N) {
-                if (!have) load_A(A, i);
+                if (!have) qm_load_half<NB>(A, p.Hs, lane, i, 0);
                 const int inx = r < 3 ? nd(r + 1) : N;
                 have = inx < N;
                 node(A, Bq, qC, i, have ? inx : -1, base + nidx * 32, 4 * (nidx & 3));
@@ -621,9 +632,9 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel_ts(const QmParams p
                     const int tb = (warp + 1) >> 1;                       // 0, 1, 1, 2, 2, 3, 3
                     const int i = warp == 0 ? 0 : (tb << lgS) - (warp & 1);   // 0, S-1, S, 2S-1, 2S, 3S-1, 3S
                     if (i < N) {
-                        double Ab[NB][NKS], Bq[NKS], qC[NB][2];
+                        double Ab[HB][NKS], Bq[NKS], qC[NB][2];
                         load_q(Bq, qC);
-                        load_A(Ab, i);
+                        qm_load_half<NB>(Ab, p.Hs, lane, i, 0);
                         node(Ab, Bq, qC, i, -1, nullptr, 0);
                     }
                 }
@@ -718,9 +729,9 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel_ts(const QmParams p
             __syncthreads();
             for (int blk = 0; blk < nblk; ++blk) chunk_pass(blk, 0);
             if (warp == 0) {   // node 0 is in no chunk (chunks hold rows 8 blk + j + 1)
-                double Ab[NB][NKS], Bq[NKS], qC[NB][2];
+                double Ab[HB][NKS], Bq[NKS], qC[NB][2];
                 load_q(Bq, qC);
-                load_A(Ab, 0);
+                qm_load_half<NB>(Ab, p.Hs, lane, 0, 0);
                 node(Ab, Bq, qC, 0, -1, nullptr, 0);
             }
             __syncthreads();
@@ -768,9 +779,14 @@ static int launch_qm_t(QmParams p, const QmPlan &pl, const double *H, cudaStream
     size_t smem = sizeof(double) * ((size_t)lay.per_cta + (size_t)warps * lay.per_warp);
     auto kern = qm_kernel<NB, LSPG>;
     const QmTsSmem tl = QmTsSmem::make(lay);
-    // tangent rows in shared memory (v3) where the register budget allows it: with n >= 24 (NB = 4) the 32 accumulators
-    // of the contraction and the tangent fragments spill, and the version with the global scratch is faster (measured)
-    if (NB <= 3 && sizeof(double) * (size_t)tl.total <= (size_t)maxsm) {
+    // tangent rows in shared memory (v3) when the tile fits next to the per-trajectory state; BX_QM_TS=0/1 forces
+    // the choice (tuning aid)
+    bool use_ts = sizeof(double) * (size_t)tl.total <= (size_t)maxsm && NB <= QM_TS_MAX_NB;
+    if (const char *e = getenv("BX_QM_TS")) {
+        if (e[0] == '0') use_ts = false;
+        if (e[0] == '1' && sizeof(double) * (size_t)tl.total <= (size_t)maxsm) use_ts = true;
+    }
+    if (use_ts) {
         kern = qm_kernel_ts<NB, LSPG>;
         smem = sizeof(double) * (size_t)tl.total;
     }
