@@ -108,6 +108,24 @@ __global__ void __launch_bounds__(256) prom_cta_pad_kernel(int N, int n, int NC,
     Phip[idx] = (i >= 0 && i < N && j < n) ? Phi[(size_t)i * n + j] : 0.0;
 }
 
+// DMMAs of one chunk for the first NU output units of a warp (the valid units form a prefix: u grows with s)
+template <int NU>
+__device__ __forceinline__ void prom_cta_mma(double (&acc)[PC_UB][4][2], const int (&offA)[PC_UB], const int (&offB)[PC_UB],
+                                             const double *Ac, const double *Jc, int KC, int ldp, int t) {
+    for (int ks = 0; ks < KC; ks += 4) {
+        const int ro = (ks + t) * ldp;
+#pragma unroll
+        for (int s = 0; s < NU; ++s) {
+            const double a0 = Ac[ro + offA[s]], a1 = Ac[ro + offA[s] + 8];
+            const double b0 = Jc[ro + offB[s]], b1 = Jc[ro + offB[s] + 8];
+            dmma884(acc[s][0][0], acc[s][0][1], a0, b0);
+            dmma884(acc[s][1][0], acc[s][1][1], a0, b1);
+            dmma884(acc[s][2][0], acc[s][2][1], a1, b0);
+            dmma884(acc[s][3][0], acc[s][3][1], a1, b1);
+        }
+    }
+}
+
 template <bool LSPG>
 __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCtaParams p) {
     extern __shared__ __align__(16) double smem[];
@@ -241,6 +259,7 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                     double acc[PC_UB][4][2];
                     int offA[PC_UB], offB[PC_UB];
                     bool uval[PC_UB], udiag[PC_UB];
+                    int nu = 0;
 #pragma unroll
                     for (int s = 0; s < PC_UB; ++s) {
 #pragma unroll
@@ -259,6 +278,7 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                         }
                         udiag[s] = Iu == Ju;
                         offA[s] = Iu * 16 + g; offB[s] = Ju * 16 + g;
+                        nu += uval[s] ? 1 : 0;
                     }
                     __syncthreads();   // rows of phase A written
                     compute_J(0, gchunk, pass == 0);
@@ -268,19 +288,12 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                         if (c + 1 < p.nchunks) compute_J(c + 1, gchunk + c + 1, pass == 0);
                         const double *Jc = s_J + (c & 1) * lay.Jsz;
                         const double *Ac = LSPG ? Jc : s_phi + ((gchunk + c) % 3u) * lay.phisz + ldp;
-                        for (int ks = 0; ks < KC; ks += 4) {
-                            const int ro = (ks + t) * ldp;
-#pragma unroll
-                            for (int s = 0; s < PC_UB; ++s) {
-                                if (uval[s]) {
-                                    const double a0 = Ac[ro + offA[s]], a1 = Ac[ro + offA[s] + 8];
-                                    const double b0 = Jc[ro + offB[s]], b1 = Jc[ro + offB[s] + 8];
-                                    dmma884(acc[s][0][0], acc[s][0][1], a0, b0);
-                                    dmma884(acc[s][1][0], acc[s][1][1], a0, b1);
-                                    dmma884(acc[s][2][0], acc[s][2][1], a1, b0);
-                                    dmma884(acc[s][3][0], acc[s][3][1], a1, b1);
-                                }
-                            }
+                        switch (nu) {
+                            case 1: prom_cta_mma<1>(acc, offA, offB, Ac, Jc, KC, ldp, t); break;
+                            case 2: prom_cta_mma<2>(acc, offA, offB, Ac, Jc, KC, ldp, t); break;
+                            case 3: prom_cta_mma<3>(acc, offA, offB, Ac, Jc, KC, ldp, t); break;
+                            case 4: prom_cta_mma<4>(acc, offA, offB, Ac, Jc, KC, ldp, t); break;
+                            default: break;
                         }
                         __syncthreads();
                     }
