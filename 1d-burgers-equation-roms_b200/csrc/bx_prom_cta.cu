@@ -330,9 +330,15 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                 __syncthreads();
 
                 // ================= phase C: blocked LU of [Ar | br], one row per thread ==========
+                // Only the PW = ceil(n / 32) warps that own matrix rows take part in the panel factorisation and the
+                // back substitution; they synchronise on named barrier 1, the other warps wait at the CTA barrier.
+                const int PW = (n + 31) >> 5;
+                const bool roww = warp < PW;
+                auto rowsync = [&]() { asm volatile("bar.sync 1, %0;" ::"r"(PW * 32) : "memory"); };
                 bool done = tid >= n;
                 for (int k0 = 0; k0 < n; k0 += 8) {
                     const int w = n - k0 < 8 ? n - k0 : 8;
+                  if (roww) {
                     const bool doneprev = done;
                     double pv[8];
 #pragma unroll
@@ -354,10 +360,10 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                                     cd[0] = __longlong_as_double(ball ? (long long)(((unsigned long long)mhi << 32) | mlo) : 0ll);
                                     cd[1] = (double)(ball ? (warp << 5) + (__ffs(ball) - 1) : -1);
                                 }
-                                __syncthreads();
+                                rowsync();
                                 unsigned long long best = 0ull;
                                 win = -1;
-                                for (int ww = 0; ww < W; ++ww) {
+                                for (int ww = 0; ww < PW; ++ww) {
                                     const double *cd = s_cand + (j & 1) * 2 * PC_MAXW + 2 * ww;
                                     const unsigned long long kk = (unsigned long long)__double_as_longlong(cd[0]);
                                     if (kk > best) { best = kk; win = (int)cd[1]; }
@@ -370,7 +376,7 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                                 done = true;
                                 s_pivrow[k0 + j] = tid;
                             }
-                            __syncthreads();
+                            rowsync();
                             if (!done) {
                                 const double *pr = s_prow + (j & 1) * 8;
                                 const double l = pv[j] * rcp(pr[j]);
@@ -391,7 +397,7 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                     } else {
                         const unsigned act = __ballot_sync(FULL, !done);
                         if (lane == 0) s_cnt[warp] = __popc(act);
-                        __syncthreads();
+                        rowsync();
                         if (!done) {
                             pos = __popc(act & ((1u << lane) - 1u));
                             for (int ww = 0; ww < warp; ++ww) pos += s_cnt[ww];
@@ -403,6 +409,7 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                         Lr[2] = make_double2(pv[4], pv[5]); Lr[3] = make_double2(pv[6], pv[7]);
                         s_act[pos] = tid;
                     }
+                  }
                     __syncthreads();
                     const int nact = n - (k0 + w);
                     // U12 column in registers, then the rank-w update of the rows still in play
@@ -450,7 +457,7 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                     int pr = 0;
                     double y = 0.0;
                     if (tid < n) { pr = s_pivrow[tid]; y = mat[pr * ldm + n]; }
-                    for (int k0 = ((n - 1) >> 3) << 3; k0 >= 0; k0 -= 8) {
+                    for (int k0 = ((n - 1) >> 3) << 3; roww && k0 >= 0; k0 -= 8) {
                         const int w = n - k0 < 8 ? n - k0 : 8;
                         if (warp == (k0 >> 5)) {
                             const int l0 = k0 & 31;
@@ -461,13 +468,14 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                                 if (lane == l0 + j) s_x[k0 + j] = xj;
                             }
                         }
-                        __syncthreads();
+                        rowsync();
                         if (tid < k0) {
 #pragma unroll
                             for (int j = 0; j < 8; ++j)
                                 if (j < w) y = fma(-mat[pr * ldm + k0 + j], s_x[k0 + j], y);
                         }
                     }
+                    __syncthreads();   // x complete for everybody
                 }
                 // ================= phase D: q = q0 + dq, error, lift (:770-776) ====================
                 double err;
