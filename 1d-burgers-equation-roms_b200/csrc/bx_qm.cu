@@ -455,7 +455,11 @@ struct QmTsSmem {
     }
 };
 
-template <int NB, bool LSPG>
+// CB = 0: tangent rows through the shared tile, one 8-step block per chunk (above).  CB > 0: through the global
+// scratch in chunks of CB blocks, produced TWO chunks ahead of the contraction (so its register ring may read into
+// the next chunk): only 3 chunks of rows are live at a time and they stay in L2 — for the mode counts whose
+// accumulators leave no room for the shared tile's extra pressure (NB = 4).
+template <int NB, bool LSPG, int CB>
 __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel_ts(const QmParams p) {
     constexpr int NC = NB * 8;
     constexpr int NKS = 2 * NB;
@@ -469,8 +473,10 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel_ts(const QmParams p
     const QmSmem lay = QmSmem::make(NP);
     const QmTsSmem tl = QmTsSmem::make(lay);
     constexpr int TSTR = 32 * 32 + 2;
+    constexpr int CBB = CB ? CB : 1;       // blocks per chunk
+    constexpr int LA = CB ? 2 : 1;         // chunks the tangent runs ahead of the contraction
     double *s_h6 = smem + lay.h6;
-    double *s_T = smem + tl.T;
+    double *s_T = smem + tl.T;             // (CB = 0 only)
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int t = lane & 3, g = lane >> 2;
@@ -556,25 +562,28 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel_ts(const QmParams p
     };
     // tangent rows of chunk blk into shared buffer `buf`: this warp takes rows nidx = warp, warp + 8, +16, +24
     // (node index grows with r, so the rows past N form a tail)
-    auto chunk_pass = [&](int blk, int buf) {
-        double *base = s_T + buf * (QM_MAXW * TSTR);
+    const int nch = (nblk + CBB - 1) / CBB;
+    auto chunk_pass = [&](int c, int buf) {
+        double *base = CB ? nullptr : s_T + buf * (QM_MAXW * TSTR);
         double A[HB][NKS], Bq[NKS], qC[NB][2];
         load_q(Bq, qC);
-        auto nd = [&](int r) { const int nidx = warp + 8 * r; return ((nidx & 3) << lgS) + (blk << 3) + (nidx >> 2) + 1; };
+        auto nd = [&](int r) { const int nidx = warp + 8 * r; return ((nidx & 3) << lgS) + c * (8 * CBB) + (nidx >> 2) + 1; };
         bool have = false;
 #pragma unroll
-        for (int r = 0; r < 4; ++r) {
+        for (int r = 0; r < 4 * CBB; ++r) {
             const int nidx = warp + 8 * r, i = nd(r);
             if (i < N) {
                 if (!have) qm_load_half<NB>(A, p.Hs, lane, i, 0);
-                const int inx = r < 3 ? nd(r + 1) : N;
+                const int inx = r < 4 * CBB - 1 ? nd(r + 1) : N;
                 have = inx < N;
-                node(A, Bq, qC, i, have ? inx : -1, base + nidx * 32, 4 * (nidx & 3));
+                node(A, Bq, qC, i, have ? inx : -1, CB ? nullptr : base + nidx * 32, 4 * (nidx & 3));
             } else {
                 have = false;
-                double *d = base + nidx * 32 + lane;   // all 32 columns (the swizzle permutes within a row)
+                if (!CB) {
+                    double *d = base + nidx * 32 + lane;   // all 32 columns (the swizzle permutes within a row)
 #pragma unroll
-                for (int tr = 0; tr < QM_MAXW; ++tr) d[tr * TSTR] = 0.0;
+                    for (int tr = 0; tr < QM_MAXW; ++tr) d[tr * TSTR] = 0.0;
+                }   // (global scratch: rows past N were zeroed once and are never written)
             }
         }
     };
@@ -639,6 +648,7 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel_ts(const QmParams p
                     }
                 }
                 chunk_pass(0, 0);
+                if (LA == 2 && nch > 1) chunk_pass(1, 1);
                 __syncthreads();
                 double acc[TILES][2];
 #pragma unroll
@@ -649,32 +659,54 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel_ts(const QmParams p
                     pm[b] = t_run[-32 + b * 8 + g];
                     p0[b] = t_run[b * 8 + g];
                 }
-                for (int blk = 0; blk < nblk; ++blk) {
-                    if (blk + 1 < nblk) chunk_pass(blk + 1, (blk + 1) & 1);
+                for (int c = 0; c < nch; ++c) {
+                    if (c + LA < nch) chunk_pass(c + LA, (c + LA) & 1);
                     if (!done) {
-                        const PromRow cur = prom_row(rc, run0 + (blk << 3) + g, ubase + (blk << 3) + g);
-                        const double *Tb = s_T + (blk & 1) * (QM_MAXW * TSTR) + myT;
+                        const int bend = (c + 1) * CBB < nblk ? (c + 1) * CBB : nblk;
+                        // the ring is refilled per chunk so that it is not live across the tangent pass above
+                        double ring[CB ? QM_PF : 1][NB];
+                        if (CB) {
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) {
+                            for (int b = 0; b < NB; ++b) {
 #pragma unroll
-                            for (int b = 0; b < NB; ++b) pp[b] = Tb[j * 128 + ((b * 8 + g) ^ (4 * t))];
-                            const int src = 4 * j + t;
-                            const double ra = shfl_idx(cur.a, src), rb = shfl_idx(cur.b, src);
-                            const double rcc = shfl_idx(cur.c, src), rR = shfl_idx(cur.R, src);
-                            double jp[NB];
-#pragma unroll
-                            for (int b = 0; b < NB; ++b) jp[b] = fma(ra, pm[b], fma(rb, p0[b], rcc * pp[b]));
-                            if (g == gR) jp[NB - 1] = rR;
-#pragma unroll
-                            for (int I = 0; I < NB; ++I) {
-#pragma unroll
-                                for (int J = LSPG ? I : 0; J < NB; ++J) {
-                                    const int ti = Tl::index(I, J);
-                                    dmma884(acc[ti][0], acc[ti][1], LSPG ? jp[I] : p0[I], jp[J]);
-                                }
+                                for (int r = 0; r < QM_PF; ++r)
+                                    ring[r][b] = t_run[(size_t)(c * CBB * 8 + r + 1) * 32 + b * 8 + g];
                             }
+                        }
+                        for (int blk = c * CBB; blk < bend; ++blk) {
+                            const PromRow cur = prom_row(rc, run0 + (blk << 3) + g, ubase + (blk << 3) + g);
+                            const double *Tb = s_T + (blk & 1) * (QM_MAXW * TSTR) + myT;
 #pragma unroll
-                            for (int b = 0; b < NB; ++b) { pm[b] = p0[b]; p0[b] = pp[b]; }
+                            for (int j = 0; j < 8; ++j) {
+                                if (CB) {   // register ring QM_PF node steps ahead (rows of the next chunk are complete)
+                                    const double *rp = t_run + (size_t)((blk << 3) + j + 1 + QM_PF) * 32;
+#pragma unroll
+                                    for (int b = 0; b < NB; ++b) {
+                                        pp[b] = ring[j % QM_PF][b];
+                                        ring[j % QM_PF][b] = rp[b * 8 + g];
+                                    }
+                                } else {
+#pragma unroll
+                                    for (int b = 0; b < NB; ++b) pp[b] = Tb[j * 128 + ((b * 8 + g) ^ (4 * t))];
+                                }
+                                const int src = 4 * j + t;
+                                const double ra = shfl_idx(cur.a, src), rb = shfl_idx(cur.b, src);
+                                const double rcc = shfl_idx(cur.c, src), rR = shfl_idx(cur.R, src);
+                                double jp[NB];
+#pragma unroll
+                                for (int b = 0; b < NB; ++b) jp[b] = fma(ra, pm[b], fma(rb, p0[b], rcc * pp[b]));
+                                if (g == gR) jp[NB - 1] = rR;
+#pragma unroll
+                                for (int I = 0; I < NB; ++I) {
+#pragma unroll
+                                    for (int J = LSPG ? I : 0; J < NB; ++J) {
+                                        const int ti = Tl::index(I, J);
+                                        dmma884(acc[ti][0], acc[ti][1], LSPG ? jp[I] : p0[I], jp[J]);
+                                    }
+                                }
+#pragma unroll
+                                for (int b = 0; b < NB; ++b) { pm[b] = p0[b]; p0[b] = pp[b]; }
+                            }
                         }
                     }
                     __syncthreads();
@@ -727,7 +759,7 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel_ts(const QmParams p
             }
             // ---- u = decoder(q) at the final q of every trajectory (:1163 / :1130): tangent-only pass -----
             __syncthreads();
-            for (int blk = 0; blk < nblk; ++blk) chunk_pass(blk, 0);
+            for (int c = 0; c < nch; ++c) chunk_pass(c, 0);
             if (warp == 0) {   // node 0 is in no chunk (chunks hold rows 8 blk + j + 1)
                 double Ab[HB][NKS], Bq[NKS], qC[NB][2];
                 load_q(Bq, qC);
@@ -779,16 +811,20 @@ static int launch_qm_t(QmParams p, const QmPlan &pl, const double *H, cudaStream
     size_t smem = sizeof(double) * ((size_t)lay.per_cta + (size_t)warps * lay.per_warp);
     auto kern = qm_kernel<NB, LSPG>;
     const QmTsSmem tl = QmTsSmem::make(lay);
-    // tangent rows in shared memory (v3) when the tile fits next to the per-trajectory state; BX_QM_TS=0/1 forces
-    // the choice (tuning aid)
-    bool use_ts = sizeof(double) * (size_t)tl.total <= (size_t)maxsm && NB <= QM_TS_MAX_NB;
+    // v3 with the shared tile for NB <= QM_TS_MAX_NB (when it fits), else v2.  The chunked-global variant of v3 is kept
+    // for A/B runs only: measured slower than v2 at n = 28 (4.8 / 5.1 vs 5.3 / 5.7 M it/s, profiles/r02n_qm_modes.txt).
+    // BX_QM_TS = 0 (v2) / 1 (shared tile) / 2 (chunked global) forces a choice.
+    int mode = (sizeof(double) * (size_t)tl.total <= (size_t)maxsm && NB <= QM_TS_MAX_NB) ? 1 : 0;
     if (const char *e = getenv("BX_QM_TS")) {
-        if (e[0] == '0') use_ts = false;
-        if (e[0] == '1' && sizeof(double) * (size_t)tl.total <= (size_t)maxsm) use_ts = true;
+        if (e[0] == '0') mode = 0;
+        if (e[0] == '1' && sizeof(double) * (size_t)tl.total <= (size_t)maxsm) mode = 1;
+        if (e[0] == '2') mode = 2;
     }
-    if (use_ts) {
-        kern = qm_kernel_ts<NB, LSPG>;
+    if (mode == 1) {
+        kern = qm_kernel_ts<NB, LSPG, 0>;
         smem = sizeof(double) * (size_t)tl.total;
+    } else if (mode == 2) {
+        kern = qm_kernel_ts<NB, LSPG, 2>;
     }
     BX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     long long ctas = pl.sms;
