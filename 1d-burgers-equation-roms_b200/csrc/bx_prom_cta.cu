@@ -2,7 +2,7 @@
 // FEMBurgers.pod_prom_burgers (FEM/fem_burgers.py:709-785), Galerkin and LSPG.  The reference's own driver
 // runs 40 modes (POD/Results_thesis/prom_pod.py:35, tol 1e-3) and its stored truncations go up to 227.
 //
-// One CTA (4, 8 or 16 warps) integrates one trajectory; CTAs pull samples from an atomic queue.  The basis
+// One CTA (8 or 16 warps) integrates one trajectory; CTAs pull samples from an atomic queue.  The basis
 // Phi (N x n, up to 0.9 MB) no longer fits next to the work tiles, so it streams from L2 in chunks of KC nodes
 // (a zero-padded N x NC copy of Phi in the workspace, rows moved by 1-D bulk copies of the TMA engine into a
 // three-deep mbarrier ring); the state, the bands and the n x n reduced system stay in shared memory for the
