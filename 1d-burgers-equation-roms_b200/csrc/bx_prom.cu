@@ -451,10 +451,15 @@ static long long prom_forcing_bytes(int B, int N) {
 extern "C" long long bx_prom_workspace_bytes(int B, int N, int n) {
     if (B < 0 || N < 2 || n < 1) return -1;
     long long mat = 0;
-    if (n >= 32 && n <= 240) {
-        if (bx::launch_prom_cta(B, N, n, 0, nullptr, nullptr, 0, nullptr, nullptr, 0.0, 0.0, nullptr, BX_GALERKIN, 0.0, 1,
-                                nullptr, nullptr, nullptr, 0, nullptr, &mat) != BX_OK)
-            return -1;
+    if (n >= 32 && n <= 240) {   // the two projections pick different launch shapes: size for the larger need
+        static const int projs[2] = {BX_GALERKIN, BX_LSPG};
+        for (int pi = 0; pi < 2; ++pi) {
+            long long m = 0;
+            if (bx::launch_prom_cta(B, N, n, 0, nullptr, nullptr, 0, nullptr, nullptr, 0.0, 0.0, nullptr, projs[pi], 0.0, 1,
+                                    nullptr, nullptr, nullptr, 0, nullptr, &m) != BX_OK)
+                return -1;
+            if (m > mat) mat = m;
+        }
     }
     return prom_forcing_bytes(B, N) + mat;
 }

@@ -59,7 +59,7 @@ struct PromCtaSmem {
     int h6, u, bn, hfs, row, bar, q, q0, x, prow, cand, red2, ints, work, phi, J, L, red, mat, total;
     int arr, phisz, Jsz;
     __host__ __device__ static PromCtaSmem make(int N, int n, int NC, int ldp, int ldm, int KC, int NPad, int lgS,
-                                                int W, int mat_in_smem) {
+                                                int W, int mat_in_smem, int NS) {
         PromCtaSmem m;
         const int S = 1 << lgS;
         m.arr = S + 4;
@@ -83,8 +83,8 @@ struct PromCtaSmem {
         // chunk ring
         m.phisz = (KC + 2) * ldp;
         m.Jsz = KC * ldp;
-        m.phi = o; m.J = o + 3 * m.phisz;
-        o += 3 * m.phisz + 2 * m.Jsz;
+        m.phi = o; m.J = o + NS * m.phisz;   // NS ring slots: 3 (Galerkin reads Phi rows in the DMMA), 2 (LSPG)
+        o += NS * m.phisz + 2 * m.Jsz;
         o = (o + 1) & ~1;
         // the ring is refilled for the next contraction while the LU runs, so these do not alias it
         m.L = o;                             // packed L21 panel, NC x 8, 16-byte aligned rows
@@ -134,7 +134,11 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
     const int T = blockDim.x, W = T >> 5;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int t = lane & 3, g = lane >> 2;
-    const PromCtaSmem lay = PromCtaSmem::make(N, n, NC, ldp, ldm, KC, p.NPad, lgS, W, p.mat_global ? 0 : 1);
+    // LSPG contracts J with itself, so a Phi chunk is dead once its J rows exist: two ring slots are enough
+    // (chunk c + 2 lands in the slot chunk c was read from one barrier earlier); Galerkin still reads chunk c
+    // as the left operand while c + 1 feeds the J pass and c + 2 is in flight
+    constexpr unsigned NS = LSPG ? 2u : 3u;
+    const PromCtaSmem lay = PromCtaSmem::make(N, n, NC, ldp, ldm, KC, p.NPad, lgS, W, p.mat_global ? 0 : 1, (int)NS);
     double *s_h6 = smem + lay.h6, *s_u = smem + lay.u, *s_bn = smem + lay.bn, *s_hfs = smem + lay.hfs;
     double2 *s_row = reinterpret_cast<double2 *>(smem + lay.row);
     uint64_t *s_bar = reinterpret_cast<uint64_t *>(smem + lay.bar);
@@ -152,7 +156,7 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
         for (int b = 0; b < 3; ++b) mbar_init(&s_bar[b], 1);
         fence_mbar_init();
     }
-    unsigned gchunk = 0;   // chunks staged so far (ring slot = gchunk % 3, parity = (gchunk / 3) & 1)
+    unsigned gchunk = 0;   // chunks staged so far (ring slot = gchunk % NS, parity = (gchunk / NS) & 1)
     __syncthreads();
     for (int e = tid; e <= N - 2; e += T) s_h6[sk(e, S, lgS)] = (p.X[e + 1] - p.X[e]) / 6.0;
 
@@ -169,7 +173,7 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
     // stage the KC + 2 Phi rows of chunk c (global number gc): one bulk copy per row, issued by warp 0
     auto stage_phi = [&](int c, unsigned gc) {
         if (warp == 0) {
-            const unsigned slot = gc % 3u;
+            const unsigned slot = gc % NS;
             fence_proxy_async();   // the ring aliases buffers the generic proxy wrote (L21 panel, partial q0)
             if (lane == 0) mbar_arrive_expect_tx(&s_bar[slot], (uint32_t)((KC + 2) * NC * 8));
             __syncwarp();
@@ -190,8 +194,8 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
         __syncthreads();
         const int smp = s_cnt[W];
         if (smp >= p.B) {   // drain the two chunks in flight before the CTA gives up its shared memory
-            mbar_wait(&s_bar[gchunk % 3u], (gchunk / 3u) & 1u);
-            if (p.nchunks > 1) mbar_wait(&s_bar[(gchunk + 1) % 3u], ((gchunk + 1) / 3u) & 1u);
+            mbar_wait(&s_bar[gchunk % NS], (gchunk / NS) & 1u);
+            if (p.nchunks > 1) mbar_wait(&s_bar[(gchunk + 1) % NS], ((gchunk + 1) / NS) & 1u);
             break;
         }
         rc.mu1 = p.mu1[smp];
@@ -233,10 +237,10 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                 // ================= phase B: J = A Phi, contraction (:756-762) ====================
                 double q0acc = 0.0;
                 auto compute_J = [&](int c, unsigned gc, bool with_q0) {
-                    mbar_wait(&s_bar[gc % 3u], (gc / 3u) & 1u);
+                    mbar_wait(&s_bar[gc % NS], (gc / NS) & 1u);
                     if (jact) {
                         const int kk0 = jrr * RPT;
-                        const double *ph = s_phi + (gc % 3u) * lay.phisz + kk0 * ldp + jcol;
+                        const double *ph = s_phi + (gc % NS) * lay.phisz + kk0 * ldp + jcol;
                         double *jr = s_J + (c & 1) * lay.Jsz + kk0 * ldp + jcol;
                         const double2 *rw = s_row + 2 * (c * KC + kk0);
                         const double *up = s_u + c * KC + kk0 + 2;   // sk(i) = i + 2 for 0 <= i < S
@@ -287,7 +291,7 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                         if (c + 2 < p.nchunks) stage_phi(c + 2, gchunk + c + 2);
                         if (c + 1 < p.nchunks) compute_J(c + 1, gchunk + c + 1, pass == 0);
                         const double *Jc = s_J + (c & 1) * lay.Jsz;
-                        const double *Ac = LSPG ? Jc : s_phi + ((gchunk + c) % 3u) * lay.phisz + ldp;
+                        const double *Ac = LSPG ? Jc : s_phi + ((gchunk + c) % NS) * lay.phisz + ldp;
                         switch (nu) {
                             case 1: prom_cta_mma<1>(acc, offA, offB, Ac, Jc, KC, ldp, t); break;
                             case 2: prom_cta_mma<2>(acc, offA, offB, Ac, Jc, KC, ldp, t); break;
@@ -567,6 +571,7 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
     BX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     BX_CUDA(cudaDeviceGetAttribute(&maxsm, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
     static const int kcs[3] = {32, 16, 8};
+    const int NS = projection == BX_LSPG ? 2 : 3;
     PromCtaSmem lay;
     bool found = false;
     int W = Wmin;
@@ -578,7 +583,7 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
                 const int kc = kcs[ki];
                 if (force_kc && kc != force_kc) continue;
                 const int nch = (N + kc - 1) / kc;
-                const PromCtaSmem l = PromCtaSmem::make(N, n, p.NC, p.ldp, p.ldm, kc, nch * kc, p.lgS, w, mg ? 0 : 1);
+                const PromCtaSmem l = PromCtaSmem::make(N, n, p.NC, p.ldp, p.ldm, kc, nch * kc, p.lgS, w, mg ? 0 : 1, NS);
                 const long long bytes = (long long)l.total * (long long)sizeof(double);
                 if (bytes > (long long)maxsm) continue;
                 int o = (int)(233472LL / (bytes + 1024));
@@ -594,7 +599,7 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
             p.nchunks = (N + p.KC - 1) / p.KC;
             p.NPad = p.nchunks * p.KC;
             p.mat_global = mg;
-            lay = PromCtaSmem::make(N, n, p.NC, p.ldp, p.ldm, p.KC, p.NPad, p.lgS, W, mg ? 0 : 1);
+            lay = PromCtaSmem::make(N, n, p.NC, p.ldp, p.ldm, p.KC, p.NPad, p.lgS, W, mg ? 0 : 1, NS);
         }
     }
     p.passes = (p.units + W * PC_UB - 1) / (W * PC_UB);

@@ -164,8 +164,22 @@ class HostSweepBuffers:
         self.d2h_bytes = 0
 
 
+def chunk_schedule(B, chunk, ramp=True):
+    """[(lo, hi), ...] covering range(B) in pieces of at most `chunk` samples.  With ramp the first pieces are
+    chunk/4 and chunk/2 long, so the device->host copy (the bound of a host-streaming sweep) starts after a
+    quarter-size kernel instead of a full one; the copy engine is then busy until the end."""
+    out, lo = [], 0
+    sizes = [max(1, chunk // 4), max(1, chunk // 2)] if ramp and B > chunk else []
+    while lo < B:
+        n = sizes.pop(0) if sizes else chunk
+        hi = min(B, lo + n)
+        out.append((lo, hi))
+        lo = hi
+    return out
+
+
 def fom_sweep_to_host(fem, At, nTimeSteps, u0, mu1, mu2, E=0.0, chunk=1024, consumer=None,
-                      buffers: HostSweepBuffers | None = None, tol=1e-6, kmax=20):
+                      buffers: HostSweepBuffers | None = None, tol=1e-6, kmax=20, ramp=True):
     """FOM sweep with HOST inputs and HOST outputs.
 
     mu1, mu2: pinned (or pageable) host float64 tensors / numpy arrays of shape (B,).
@@ -202,8 +216,7 @@ def fom_sweep_to_host(fem, At, nTimeSteps, u0, mu1, mu2, E=0.0, chunk=1024, cons
             consumer(lo, hi, buf.hU[i][: hi - lo], buf.hIt[i][: hi - lo])
         pending[i] = None
 
-    for c, lo in enumerate(range(0, B, chunk)):
-        hi = min(B, lo + chunk)
+    for c, (lo, hi) in enumerate(chunk_schedule(B, chunk, ramp)):
         n = hi - lo
         i = c & 1
         drain(i)  # host + device buffer i are free again
