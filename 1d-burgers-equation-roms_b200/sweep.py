@@ -164,10 +164,13 @@ class HostSweepBuffers:
         self.d2h_bytes = 0
 
 
-def chunk_schedule(B, chunk, ramp=True):
+def chunk_schedule(B, chunk, ramp=False):
     """[(lo, hi), ...] covering range(B) in pieces of at most `chunk` samples.  With ramp the first pieces are
     chunk/4 and chunk/2 long, so the device->host copy (the bound of a host-streaming sweep) starts after a
-    quarter-size kernel instead of a full one; the copy engine is then busy until the end."""
+    quarter-size kernel instead of a full one.  Measured on B200 (tools/e2e_time.py): a 256-sample kernel takes
+    as long as a 1024-sample one (a trajectory is a serial chain of ~6000 Picard iterations, ~14 ms), so the ramp
+    only pays for chunks of 2048 and more; 512-sample chunks without ramp are the fastest (171 ms against the
+    155 ms the 8.4 GB take at the box's 54 GB/s pinned D2H rate)."""
     out, lo = [], 0
     sizes = [max(1, chunk // 4), max(1, chunk // 2)] if ramp and B > chunk else []
     while lo < B:
@@ -179,7 +182,7 @@ def chunk_schedule(B, chunk, ramp=True):
 
 
 def fom_sweep_to_host(fem, At, nTimeSteps, u0, mu1, mu2, E=0.0, chunk=1024, consumer=None,
-                      buffers: HostSweepBuffers | None = None, tol=1e-6, kmax=20, ramp=True):
+                      buffers: HostSweepBuffers | None = None, tol=1e-6, kmax=20, ramp=False):
     """FOM sweep with HOST inputs and HOST outputs.
 
     mu1, mu2: pinned (or pageable) host float64 tensors / numpy arrays of shape (B,).

@@ -258,7 +258,7 @@ def main():
     # ---- end-to-end leg: host parameters in, host snapshots out, through the public sweep API ----
     e2e = None
     if not args.no_e2e:
-        chunk = min(1024, B)
+        chunk = min(512, B)     # fastest on B200 (tools/e2e_time.py): D2H of a chunk hides the next chunk's kernel
         bufs = bsweep.HostSweepBuffers(fem, chunk, nT)
         h1 = torch.from_numpy(m1).pin_memory(); h2 = torch.from_numpy(m2).pin_memory()
         check = []

@@ -91,3 +91,19 @@ def test_reference_file_names_and_npy_writer(tmp_path):
     it = np.arange(12, dtype=np.int32).reshape(3, 4)
     sweep._write_npy(str(tmp_path / "it.npy"), it)
     assert np.array_equal(np.load(tmp_path / "it.npy"), it)
+
+
+@pytest.mark.parametrize("B,chunk", [(0, 512), (1, 512), (511, 512), (512, 512), (513, 512), (4096, 512), (4097, 1024), (5000, 2048)])
+@pytest.mark.parametrize("ramp", [False, True])
+def test_chunk_schedule_covers_the_sweep(B, chunk, ramp):
+    """Host logic of the host-streaming sweep: the pieces tile range(B) in order, none is empty or longer than
+    the buffers, and with ramp the copy starts after a quarter-size piece."""
+    from burgers_b200 import sweep
+    pieces = sweep.chunk_schedule(B, chunk, ramp)
+    assert [lo for lo, _ in pieces] == [0] * min(B, 1) + [hi for _, hi in pieces[:-1]]
+    assert all(0 < hi - lo <= chunk for lo, hi in pieces)
+    assert (pieces[-1][1] if pieces else 0) == B
+    if ramp and B > chunk:
+        assert pieces[0] == (0, chunk // 4) and pieces[1] == (chunk // 4, chunk // 4 + chunk // 2)
+    elif B:
+        assert pieces[0] == (0, min(B, chunk))
