@@ -124,14 +124,19 @@ def measured_peak_hbm():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def ncu_traffic():
+def ncu_capture(key="fom_picard_kernel_dram_bytes_per_launch"):
+    """A number of the committed ncu --set full capture of the FOM kernel (profiles/roofline_traffic.json)."""
     p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(p):
         try:
-            return json.load(open(p)).get("fom_picard_kernel_dram_bytes_per_launch")
+            return json.load(open(p)).get(key)
         except Exception:
             return None
     return None
+
+
+def ncu_traffic():
+    return ncu_capture()
 
 
 # ----------------------------------------------------------------------------------------------
@@ -296,7 +301,8 @@ def main():
     k_ms = float(np.mean(per_launch_ms))
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": ncu_traffic(), "peak_source": peak_src, "kernel": "bx::fom_picard_kernel<16,4,3>",
+                "traffic": ncu_traffic(), "peak_source": peak_src,
+                "fp64_pipe_active_pct_ncu": ncu_capture("fp64_pipe_cycles_active_pct"), "kernel": "bx::fom_picard_kernel<16,4,3>",
                 "kernel_ms": k_ms, "algorithmic_bytes_per_launch": alg_bytes,
                 "model": "88*N B per Picard iteration + 8*N B per time step per sample (banded dataflow of SURVEY 8d); "
                          "the fused kernel keeps the bands in registers, so its real DRAM traffic is ~8*N per step "
