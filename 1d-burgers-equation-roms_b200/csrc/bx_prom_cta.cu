@@ -561,7 +561,7 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
         int w = 0, kc = 0;
         if (sscanf(e, "%d,%d", &w, &kc) == 2) {
             if ((w == 8 || w == 16) && w >= Wmin) force_w = w;
-            if (kc == 8 || kc == 16 || kc == 32) force_kc = kc;
+            if (kc == 8 || kc == 12 || kc == 16 || kc == 24 || kc == 32) force_kc = kc;
         }
     }
     p.lgS = 3;
@@ -570,7 +570,7 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
     BX_CUDA(cudaGetDevice(&dev));
     BX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     BX_CUDA(cudaDeviceGetAttribute(&maxsm, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
-    static const int kcs[3] = {32, 16, 8};
+    static const int kcs[5] = {32, 24, 16, 12, 8};   // multiples of 4 (DMMA k-steps), <= 32 (workspace rows)
     const int NS = projection == BX_LSPG ? 2 : 3;
     PromCtaSmem lay;
     bool found = false;
@@ -579,7 +579,7 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
         int best_score = 0, best_kc = 0, best_w = 0;
         for (int w = Wmin; w <= PC_MAXW; w *= 2) {
             if (force_w && w != force_w) continue;
-            for (int ki = 0; ki < 3; ++ki) {
+            for (int ki = 0; ki < 5; ++ki) {
                 const int kc = kcs[ki];
                 if (force_kc && kc != force_kc) continue;
                 const int nch = (N + kc - 1) / kc;
