@@ -5,7 +5,7 @@
 // One CTA (8 or 16 warps) integrates one trajectory; CTAs pull samples from an atomic queue.  The basis
 // Phi (N x n, up to 0.9 MB) no longer fits next to the work tiles, so it streams from L2 in chunks of KC nodes
 // (a zero-padded N x NC copy of Phi in the workspace, rows moved by 1-D bulk copies of the TMA engine into a
-// three-deep mbarrier ring); the state, the bands and the n x n reduced system stay in shared memory for the
+// two- (LSPG) or three-slot (Galerkin) mbarrier ring); the state, the bands and the n x n reduced system stay in shared memory for the
 // whole trajectory (the reduced system moves to an L2-resident scratch when it exceeds what is left, n >~ 140).
 //
 // One nonlinear iteration (:726-781):
