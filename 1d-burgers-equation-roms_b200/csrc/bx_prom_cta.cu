@@ -75,8 +75,8 @@ struct PromCtaSmem {
         m.q0 = o; o += NC;
         m.x = o; o += NC;
         m.prow = o; o += 16;
-        m.cand = o; o += 4 * PC_MAXW;       // 2 buffers x W x (key, index)
-        m.red2 = o; o += 2 * PC_MAXW + 2;
+        m.cand = o; o += 4 * W;             // 2 buffers x W x (key, index)
+        m.red2 = o; o += 2 * W + 2;
         m.ints = o; o += NC + NC / 4 + 8;   // pivrow[NC] (int), act[NC] (int) -> NC doubles; cnt[W] + misc
         o = (o + 1) & ~1;
         m.work = o;
@@ -86,11 +86,12 @@ struct PromCtaSmem {
         m.phi = o; m.J = o + NS * m.phisz;   // NS ring slots: 3 (Galerkin reads Phi rows in the DMMA), 2 (LSPG)
         o += NS * m.phisz + 2 * m.Jsz;
         o = (o + 1) & ~1;
-        // the ring is refilled for the next contraction while the LU runs, so these do not alias it
-        m.L = o;                             // packed L21 panel, NC x 8, 16-byte aligned rows
-        m.red = o;                           // partial q0 per row run (<= 8 x NC), dead before the LU starts
-        o += NC * 8;
-        o = (o + 1) & ~1;
+        // The Phi slots are refilled for the next contraction while the LU runs, the J tiles are not: the packed
+        // L21 panel (NC x 8, 16-byte aligned rows) and the partial q0 per row run (RR x NC, RR <= KC, dead before
+        // the LU starts) live in J tile 0 (KC x ldp >= 8 NC), which is dead from the last DMMA of an iteration to
+        // the first J pass of the next.
+        m.L = m.J;
+        m.red = m.J;
         m.mat = o;
         if (mat_in_smem) o += n * ldm;
         m.total = o;
@@ -109,8 +110,8 @@ __global__ void __launch_bounds__(256) prom_cta_pad_kernel(int N, int n, int NC,
 }
 
 // DMMAs of one chunk for the first NU output units of a warp (the valid units form a prefix: u grows with s)
-template <int NU>
-__device__ __forceinline__ void prom_cta_mma(double (&acc)[PC_UB][4][2], const int (&offA)[PC_UB], const int (&offB)[PC_UB],
+template <int NU, int UB>
+__device__ __forceinline__ void prom_cta_mma(double (&acc)[UB][4][2], const int (&offA)[UB], const int (&offB)[UB],
                                              const double *Ac, const double *Jc, int KC, int ldp, int t) {
     for (int ks = 0; ks < KC; ks += 4) {
         const int ro = (ks + t) * ldp;
@@ -126,8 +127,10 @@ __device__ __forceinline__ void prom_cta_mma(double (&acc)[PC_UB][4][2], const i
     }
 }
 
-template <bool LSPG>
-__global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCtaParams p) {
+// UB = units per warp and pass.  UB = 1 (at most W = 8 units: LSPG up to 47 modes) is the light instance: 8 warps,
+// 80 registers per thread, three CTAs per SM; UB = PC_UB is the general one (128 registers, 8 or 16 warps).
+template <bool LSPG, int UB>
+__global__ void __launch_bounds__(UB == 1 ? 256 : PC_MAXW * 32, UB == 1 ? 3 : 1) prom_cta_kernel(const PromCtaParams p) {
     extern __shared__ __align__(16) double smem[];
     const int N = p.N, n = p.n, NC = p.NC, ldp = p.ldp, ldm = p.ldm, KC = p.KC, lgS = p.lgS;
     const int S = 1 << lgS;
@@ -260,15 +263,15 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                 };
 
                 for (int pass = 0; pass < p.passes; ++pass) {
-                    double acc[PC_UB][4][2];
-                    int offA[PC_UB], offB[PC_UB];
-                    bool uval[PC_UB], udiag[PC_UB];
+                    double acc[UB][4][2];
+                    int offA[UB], offB[UB];
+                    bool uval[UB], udiag[UB];
                     int nu = 0;
 #pragma unroll
-                    for (int s = 0; s < PC_UB; ++s) {
+                    for (int s = 0; s < UB; ++s) {
 #pragma unroll
                         for (int q4 = 0; q4 < 4; ++q4) { acc[s][q4][0] = 0.0; acc[s][q4][1] = 0.0; }
-                        const int u = (pass * PC_UB + s) * W + warp;
+                        const int u = (pass * UB + s) * W + warp;
                         uval[s] = u < p.units;
                         int Iu = 0, Ju = 0;
                         if (uval[s]) {
@@ -292,12 +295,16 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                         if (c + 1 < p.nchunks) compute_J(c + 1, gchunk + c + 1, pass == 0);
                         const double *Jc = s_J + (c & 1) * lay.Jsz;
                         const double *Ac = LSPG ? Jc : s_phi + ((gchunk + c) % NS) * lay.phisz + ldp;
-                        switch (nu) {
-                            case 1: prom_cta_mma<1>(acc, offA, offB, Ac, Jc, KC, ldp, t); break;
-                            case 2: prom_cta_mma<2>(acc, offA, offB, Ac, Jc, KC, ldp, t); break;
-                            case 3: prom_cta_mma<3>(acc, offA, offB, Ac, Jc, KC, ldp, t); break;
-                            case 4: prom_cta_mma<4>(acc, offA, offB, Ac, Jc, KC, ldp, t); break;
-                            default: break;
+                        if constexpr (UB == 1) {
+                            if (nu == 1) prom_cta_mma<1, UB>(acc, offA, offB, Ac, Jc, KC, ldp, t);
+                        } else {
+                            switch (nu) {
+                                case 1: prom_cta_mma<1, UB>(acc, offA, offB, Ac, Jc, KC, ldp, t); break;
+                                case 2: prom_cta_mma<2, UB>(acc, offA, offB, Ac, Jc, KC, ldp, t); break;
+                                case 3: prom_cta_mma<3, UB>(acc, offA, offB, Ac, Jc, KC, ldp, t); break;
+                                case 4: prom_cta_mma<4, UB>(acc, offA, offB, Ac, Jc, KC, ldp, t); break;
+                                default: break;
+                            }
                         }
                         __syncthreads();
                     }
@@ -306,7 +313,7 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                     if (p.nchunks > 1) stage_phi(1, gchunk + 1);
                     // accumulator tiles -> [Ar | br]; column n = br
 #pragma unroll
-                    for (int s = 0; s < PC_UB; ++s) {
+                    for (int s = 0; s < UB; ++s) {
                         if (uval[s]) {
 #pragma unroll
                             for (int q4 = 0; q4 < 4; ++q4) {
@@ -360,7 +367,7 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                                 const unsigned mlo = __reduce_max_sync(FULL, c1 ? klo : 0u);
                                 const unsigned ball = __ballot_sync(FULL, c1 && klo == mlo && !done);
                                 if (lane == 0) {
-                                    double *cd = s_cand + (j & 1) * 2 * PC_MAXW + 2 * warp;
+                                    double *cd = s_cand + (j & 1) * 2 * W + 2 * warp;
                                     cd[0] = __longlong_as_double(ball ? (long long)(((unsigned long long)mhi << 32) | mlo) : 0ll);
                                     cd[1] = (double)(ball ? (warp << 5) + (__ffs(ball) - 1) : -1);
                                 }
@@ -368,7 +375,7 @@ __global__ void __launch_bounds__(PC_MAXW * 32, 1) prom_cta_kernel(const PromCta
                                 unsigned long long best = 0ull;
                                 win = -1;
                                 for (int ww = 0; ww < PW; ++ww) {
-                                    const double *cd = s_cand + (j & 1) * 2 * PC_MAXW + 2 * ww;
+                                    const double *cd = s_cand + (j & 1) * 2 * W + 2 * ww;
                                     const unsigned long long kk = (unsigned long long)__double_as_longlong(cd[0]);
                                     if (kk > best) { best = kk; win = (int)cd[1]; }
                                 }
@@ -554,6 +561,7 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
     // (shared memory per CTA; 128 registers per thread = 512 threads per SM); ties go to the smaller CTA (more
     // trajectories in different phases per SM), then to the larger chunk (fewer barriers).  Measured on B200
     // (profiles/r02d_prom_cta_tune.txt): n = 40 -> (8, 16), n = 64 -> (8, 8), n = 96 -> (16, 16).
+    const bool light = p.units <= 8;   // one unit per warp at W = 8: the 80-register instance, three CTAs per SM
     int Wmin = 8;   // at least 8 warps: staging, the J pass and the lift are per-warp instruction bound
     while (Wmin < PC_MAXW && (Wmin * PC_UB < p.units || Wmin * 32 < p.NC)) Wmin *= 2;
     int force_w = 0, force_kc = 0;
@@ -587,7 +595,8 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
                 const long long bytes = (long long)l.total * (long long)sizeof(double);
                 if (bytes > (long long)maxsm) continue;
                 int o = (int)(233472LL / (bytes + 1024));
-                if (o > 512 / (w * 32)) o = 512 / (w * 32);
+                const int regcap = (light && w == 8) ? 3 : 512 / (w * 32);   // 80 / 128 registers per thread
+                if (o > regcap) o = regcap;
                 if (o < 1) o = 1;
                 if (o * w > best_score) { best_score = o * w; best_kc = kc; best_w = w; }
             }
@@ -602,7 +611,8 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
             lay = PromCtaSmem::make(N, n, p.NC, p.ldp, p.ldm, p.KC, p.NPad, p.lgS, W, mg ? 0 : 1, NS);
         }
     }
-    p.passes = (p.units + W * PC_UB - 1) / (W * PC_UB);
+    const int UBsel = (light && W == 8) ? 1 : PC_UB;
+    p.passes = (p.units + W * UBsel - 1) / (W * UBsel);
     if (found) {
         p.CG = 1;
         while (p.CG * 32 < p.NC) p.CG *= 2;
@@ -633,13 +643,11 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
     p.mat_ws = p.Phip + (size_t)(N + 34) * p.NC;
     const size_t smem = sizeof(double) * (size_t)lay.total;
     int occ = 0;
-    if (projection == BX_LSPG) {
-        BX_CUDA(cudaFuncSetAttribute(prom_cta_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        BX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, prom_cta_kernel<true>, W * 32, smem));
-    } else {
-        BX_CUDA(cudaFuncSetAttribute(prom_cta_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        BX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, prom_cta_kernel<false>, W * 32, smem));
-    }
+    void (*kern)(const PromCtaParams) =
+        projection == BX_LSPG ? (UBsel == 1 ? prom_cta_kernel<true, 1> : prom_cta_kernel<true, PC_UB>)
+                              : (UBsel == 1 ? prom_cta_kernel<false, 1> : prom_cta_kernel<false, PC_UB>);
+    BX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    BX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, W * 32, smem));
     if (occ < 1) {
         set_error("bx_prom_trajectories: kernel does not fit on an SM (N = %d, n = %d)", N, n);
         return BX_ERR_UNSUPPORTED;
@@ -657,8 +665,7 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
         prom_cta_pad_kernel<<<(unsigned)(((long long)rows * p.NC + 255) / 256), 256, 0, st>>>(N, n, p.NC, rows, Phi, p.Phip);
         BX_LAUNCH_CHECK();
     }
-    if (projection == BX_LSPG) prom_cta_kernel<true><<<(unsigned)ctas, W * 32, smem, st>>>(p);
-    else prom_cta_kernel<false><<<(unsigned)ctas, W * 32, smem, st>>>(p);
+    kern<<<(unsigned)ctas, W * 32, smem, st>>>(p);
     BX_LAUNCH_CHECK();
     return BX_OK;
 }
