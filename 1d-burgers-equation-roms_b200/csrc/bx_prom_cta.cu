@@ -127,10 +127,11 @@ __device__ __forceinline__ void prom_cta_mma(double (&acc)[UB][4][2], const int 
     }
 }
 
-// UB = units per warp and pass.  UB = 1 (at most W = 8 units: LSPG up to 47 modes) is the light instance: 8 warps,
-// 80 registers per thread, three CTAs per SM; UB = PC_UB is the general one (128 registers, 8 or 16 warps).
+// UB = units per warp and pass.  UB = 1 (at most W = 8 units: LSPG up to 47 modes) and UB = 2 (at most 16 units:
+// Galerkin up to 47 modes) are the light instances: 8 warps, at most 85 registers per thread, three CTAs per SM;
+// UB = PC_UB is the general one (128 registers, 8 or 16 warps).
 template <bool LSPG, int UB>
-__global__ void __launch_bounds__(UB == 1 ? 256 : PC_MAXW * 32, UB == 1 ? 3 : 1) prom_cta_kernel(const PromCtaParams p) {
+__global__ void __launch_bounds__(UB <= 2 ? 256 : PC_MAXW * 32, UB <= 2 ? 3 : 1) prom_cta_kernel(const PromCtaParams p) {
     extern __shared__ __align__(16) double smem[];
     const int N = p.N, n = p.n, NC = p.NC, ldp = p.ldp, ldm = p.ldm, KC = p.KC, lgS = p.lgS;
     const int S = 1 << lgS;
@@ -297,6 +298,9 @@ __global__ void __launch_bounds__(UB == 1 ? 256 : PC_MAXW * 32, UB == 1 ? 3 : 1)
                         const double *Ac = LSPG ? Jc : s_phi + ((gchunk + c) % NS) * lay.phisz + ldp;
                         if constexpr (UB == 1) {
                             if (nu == 1) prom_cta_mma<1, UB>(acc, offA, offB, Ac, Jc, KC, ldp, t);
+                        } else if constexpr (UB == 2) {
+                            if (nu == 2) prom_cta_mma<2, UB>(acc, offA, offB, Ac, Jc, KC, ldp, t);
+                            else if (nu == 1) prom_cta_mma<1, UB>(acc, offA, offB, Ac, Jc, KC, ldp, t);
                         } else {
                             switch (nu) {
                                 case 1: prom_cta_mma<1, UB>(acc, offA, offB, Ac, Jc, KC, ldp, t); break;
@@ -561,7 +565,7 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
     // (shared memory per CTA; 128 registers per thread = 512 threads per SM); ties go to the smaller CTA (more
     // trajectories in different phases per SM), then to the larger chunk (fewer barriers).  Measured on B200
     // (profiles/r02d_prom_cta_tune.txt): n = 40 -> (8, 16), n = 64 -> (8, 8), n = 96 -> (16, 16).
-    const bool light = p.units <= 8;   // one unit per warp at W = 8: the 80-register instance, three CTAs per SM
+    const bool light = p.units <= 16;  // one or two units per warp at W = 8: the light instances, three CTAs per SM
     int Wmin = 8;   // at least 8 warps: staging, the J pass and the lift are per-warp instruction bound
     while (Wmin < PC_MAXW && (Wmin * PC_UB < p.units || Wmin * 32 < p.NC)) Wmin *= 2;
     int force_w = 0, force_kc = 0;
@@ -583,8 +587,10 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
     PromCtaSmem lay;
     bool found = false;
     int W = Wmin;
+    int best_o = 0;   // CTAs per SM the chosen shape was scored with
     for (int mg = 0; mg < 2 && !found; ++mg) {   // reduced system in shared memory if it fits at all
         int best_score = 0, best_kc = 0, best_w = 0;
+        best_o = 0;
         for (int w = Wmin; w <= PC_MAXW; w *= 2) {
             if (force_w && w != force_w) continue;
             for (int ki = 0; ki < 5; ++ki) {
@@ -598,7 +604,7 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
                 const int regcap = (light && w == 8) ? 3 : 512 / (w * 32);   // 80 / 128 registers per thread
                 if (o > regcap) o = regcap;
                 if (o < 1) o = 1;
-                if (o * w > best_score) { best_score = o * w; best_kc = kc; best_w = w; }
+                if (o * w > best_score) { best_score = o * w; best_kc = kc; best_w = w; best_o = o; }
             }
         }
         if (best_score > 0) {
@@ -611,7 +617,9 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
             lay = PromCtaSmem::make(N, n, p.NC, p.ldp, p.ldm, p.KC, p.NPad, p.lgS, W, mg ? 0 : 1, NS);
         }
     }
-    const int UBsel = (light && W == 8) ? 1 : PC_UB;
+    // the light instances pay only where a third CTA fits (measured: n = 64 LSPG at two CTAs per SM is 11 % slower
+    // with the 80-register build than with the general one)
+    const int UBsel = (light && W == 8 && best_o >= 3) ? (p.units <= 8 ? 1 : 2) : PC_UB;
     p.passes = (p.units + W * UBsel - 1) / (W * UBsel);
     if (found) {
         p.CG = 1;
@@ -644,8 +652,9 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
     const size_t smem = sizeof(double) * (size_t)lay.total;
     int occ = 0;
     void (*kern)(const PromCtaParams) =
-        projection == BX_LSPG ? (UBsel == 1 ? prom_cta_kernel<true, 1> : prom_cta_kernel<true, PC_UB>)
-                              : (UBsel == 1 ? prom_cta_kernel<false, 1> : prom_cta_kernel<false, PC_UB>);
+        projection == BX_LSPG
+            ? (UBsel == 1 ? prom_cta_kernel<true, 1> : UBsel == 2 ? prom_cta_kernel<true, 2> : prom_cta_kernel<true, PC_UB>)
+            : (UBsel == 1 ? prom_cta_kernel<false, 1> : UBsel == 2 ? prom_cta_kernel<false, 2> : prom_cta_kernel<false, PC_UB>);
     BX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     BX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, W * 32, smem));
     if (occ < 1) {
