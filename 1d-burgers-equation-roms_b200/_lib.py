@@ -11,6 +11,10 @@ LIB_PATH = os.path.join(PKG_DIR, "libburgers_b200.so")
 
 BX_OK, BX_ERR_INVALID, BX_ERR_CUDA, BX_ERR_UNSUPPORTED, BX_ERR_PROJECTION = 0, -1, -2, -3, -4
 BX_GALERKIN, BX_LSPG = 0, 1
+BX_PROBE_DFMA, BX_PROBE_DMMA = 0, 1
+# bx_set_tuning knobs (include/burgers_b200.h)
+TUNING_KNOBS = {"fom_warps_per_trajectory": 0, "prom_cta_warps": 1, "prom_cta_chunk": 2, "qm_schedule": 3,
+                "prom_warps_per_trajectory": 4}
 
 P = c_void_p  # device pointer / stream
 
@@ -28,7 +32,7 @@ SIGNATURES = {
     "bx_tridiag_solve_update": (c_int, [c_int, c_int, P, P, P, P, P, P, P, P]),
     "bx_workspace_bytes": (c_longlong, []),
     "bx_fom_picard_trajectories": (c_int, [c_int, c_int, c_int, P, P, c_int, P, P, c_double, c_double,
-                                           c_double, c_int, P, P, P, P]),
+                                           c_double, c_int, P, P, P, P, P]),
     "bx_fine_workspace_bytes": (c_longlong, [c_int]),
     "bx_fom_picard_finemesh": (c_int, [c_int, c_int, c_int, P, P, c_int, P, P, c_double, c_double,
                                        c_double, c_int, P, P, P, P]),
@@ -36,10 +40,14 @@ SIGNATURES = {
                                            c_double, c_double, c_int, P, P, P, P]),
     "bx_prom_workspace_bytes": (c_longlong, [c_int, c_int, c_int]),
     "bx_prom_trajectories": (c_int, [c_int, c_int, c_int, c_int, P, P, c_int, P, P, c_double, c_double,
-                                     P, c_int, c_double, c_int, P, P, P, P]),
+                                     P, c_int, c_double, c_int, P, P, P, P, P]),
     "bx_qm_workspace_bytes": (c_longlong, [c_int, c_int, c_int]),
     "bx_qm_prom_trajectories": (c_int, [c_int, c_int, c_int, c_int, P, P, c_int, P, P, c_double, c_double,
-                                        P, P, c_int, c_double, c_int, P, P, P, P]),
+                                        P, P, c_int, c_double, c_int, P, P, P, P, P]),
+    "bx_qm_schedule_available": (c_int, [c_int, c_int, c_int]),
+    "bx_set_tuning": (c_int, [c_int, c_int]),
+    "bx_get_tuning": (c_int, [c_int]),
+    "bx_probe_fp64_peak": (c_longlong, [c_int, c_int, P, P]),
     "bx_gram_workspace_bytes": (c_longlong, [c_int, c_longlong]),
     "bx_gram_accumulate": (c_int, [c_int, c_longlong, P, P, c_int, P, P]),
     "bx_snapshots_to_reference_layout": (c_int, [c_int, c_int, c_int, P, P, P]),
@@ -68,6 +76,24 @@ def load():
         fn.argtypes = args
     _lib = lib
     return lib
+
+
+def set_tuning(knob: str, value: int):
+    """Force a launch-shape choice (A/B measurements, tests that must reach every kernel instance); value < 0
+    restores the automatic choice.  Process-wide.  Replaces round 1's environment switches."""
+    if knob not in TUNING_KNOBS:
+        raise KeyError(f"unknown tuning knob {knob!r}; known: {sorted(TUNING_KNOBS)}")
+    check(load().bx_set_tuning(TUNING_KNOBS[knob], int(value)), "bx_set_tuning")
+
+
+def get_tuning(knob: str) -> int:
+    return int(load().bx_get_tuning(TUNING_KNOBS[knob]))
+
+
+def qm_schedules(N: int, n: int):
+    """Tangent-row schedules of the quadratic-manifold kernel that can run at (N, n) on the current device."""
+    lib = load()
+    return [s for s in (0, 1, 2) if lib.bx_qm_schedule_available(int(N), int(n), s) == 1]
 
 
 def check(code: int, what: str):

@@ -11,6 +11,16 @@ namespace bx {
 // ---- host: last-error text ------------------------------------------------------------
 void set_error(const char *fmt, ...);
 
+// ---- host: explicit tuning knobs (bx_set_tuning), cached device / kernel properties --------------
+int tuning(int knob);   // value of a BX_TUNE_* knob, -1 = automatic
+struct DeviceInfo { int device, sms, max_smem_optin, cooperative; };
+int device_info(DeviceInfo &out);   // properties of the current device (queried once per device)
+// opt-in shared memory + resident CTAs per SM of `kern` at (threads, smem): the runtime is asked once per
+// (kernel, device, threads, smem), later launches hit a small cache
+int kernel_occupancy(const void *kern, int threads, size_t smem, int *occ_out);
+// one of the 64 work-queue counters in the 256-byte head of a caller workspace (rotates per launch)
+unsigned int *queue_slot(void *workspace);
+
 #define BX_REQUIRE(cond, ...)                                   \
     do {                                                        \
         if (!(cond)) {                                          \
@@ -102,17 +112,26 @@ __device__ __forceinline__ double warp_pcr(double al, double be, double ga, doub
 // Partition solve, condensation part.  Input: the lane's M rows after the local normalised
 // Thomas sweep,  fs[j] P + x[j] + cs[j] x[j+1] = rs[j]  (P = previous lane's last unknown,
 // x[M] = next lane's first unknown).  Output: x[M-1] of this lane (xl) and P.
+// upward sweep of a lane's M swept rows: row 0 as  F P + x[0] + G x[M-1] = R
 template <int M>
-__device__ __forceinline__ void partition_condense(const double (&cs)[M], const double (&rs)[M],
-                                                   const double (&fs)[M], int lane, double &xl, double &P) {
-    // upward sweep: row 0 as  F P + x[0] + G x[M-1] = R
-    double F = fs[M - 2], G = cs[M - 2], R = rs[M - 2];
+__device__ __forceinline__ void partition_upward(const double (&cs)[M], const double (&rs)[M],
+                                                 const double (&fs)[M], double &F, double &G, double &R) {
+    if (M == 1) { F = fs[0]; G = 0.0; R = rs[0]; return; }   // x[0] is x[M-1]: F P + x[0] = R - cs[0] x_next, unused coupling
+    F = fs[M > 1 ? M - 2 : 0]; G = cs[M > 1 ? M - 2 : 0]; R = rs[M > 1 ? M - 2 : 0];
 #pragma unroll
     for (int j = M - 3; j >= 0; --j) {
         F = fma(-cs[j], F, fs[j]);
         G = -cs[j] * G;
         R = fma(-cs[j], R, rs[j]);
     }
+}
+
+template <int M>
+__device__ __forceinline__ void partition_condense(const double (&cs)[M], const double (&rs)[M],
+                                                   const double (&fs)[M], int lane, double &xl, double &P) {
+    static_assert(M >= 2, "a lane needs at least two rows");
+    double F, G, R;
+    partition_upward<M>(cs, rs, fs, F, G, R);
     // eliminate the next lane's x[0] from this lane's last row
     const double Fn = shfl_down(F, 1), Gn = shfl_down(G, 1), Rn = shfl_down(R, 1);
     const double cl = (lane == 31) ? 0.0 : cs[M - 1];

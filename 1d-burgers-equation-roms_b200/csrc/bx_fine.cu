@@ -46,7 +46,7 @@ struct FineParams {
     double *g_atf, *g_bn;     // FM x FT per CTA, node j at [j * FT + tid]
     double *g_rows;           // [G][8]: al, be, gaE, rho, F, G, R, -
     double *g_norm;           // [G][4]: sd, su, u_first, u_last
-    unsigned int *bar;
+    unsigned long long *bar;
 };
 
 struct Lvl { double y, z1, z2; };
@@ -112,17 +112,18 @@ __device__ __forceinline__ Lvl group_up(int m, int lane, double &al, double &be,
     return lv;
 }
 
-// all CTAs of the (co-resident, cooperative) grid; monotonic counter, target = epoch * G
-__device__ __forceinline__ void grid_barrier(unsigned int *bar, unsigned int G, unsigned int &epoch) {
+// all CTAs of the (co-resident, cooperative) grid; monotonic 64-bit counter, target = epoch * G (two barriers per
+// Picard iteration and G arrivals each: a 32-bit counter would wrap after a few thousand trajectories per launch)
+__device__ __forceinline__ void grid_barrier(unsigned long long *bar, unsigned int G, unsigned long long &epoch) {
     __syncthreads();
     if (threadIdx.x == 0) {
         ++epoch;
         __threadfence();
-        atomicAdd(bar, 1u);
-        const unsigned int target = epoch * G;
-        unsigned int v;
+        atomicAdd(bar, 1ull);
+        const unsigned long long target = epoch * G;
+        unsigned long long v;
         do {
-            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(bar) : "memory");
+            asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(bar) : "memory");
         } while (v < target);
         __threadfence();
     }
@@ -149,7 +150,7 @@ __global__ void __launch_bounds__(FT, 1) fine_fom_kernel(const FineParams p) {
     const double a6 = At / 6.0, c1 = 1.5 * At;
     const bool has_e = p.E != 0.0;
     const double ate = At * p.E;
-    unsigned int epoch = 0;
+    unsigned long long epoch = 0;
 
     double *t_h6 = p.g_h6 + (size_t)cta * (FM + 1) * FT + tid;
     double *t_hfs = p.g_hfs + (size_t)cta * (FM + 1) * FT + tid;
@@ -396,7 +397,10 @@ __global__ void __launch_bounds__(FT, 1) fine_fom_kernel(const FineParams p) {
 #pragma unroll
                 for (int j = 0; j < FM; ++j) if (node0 + j < N) Un1[j] = u[j];
             }
-            if (cta == 0 && tid == 0 && p.iters) p.iters[(long long)smp * p.nsteps + n] = k;
+            // non-finite state (config 5b: At = 0.05 on this mesh overflows): flag -1; the following steps stay
+            // non-finite and carry the flag as well (include/burgers_b200.h)
+            if (cta == 0 && tid == 0 && p.iters)
+                p.iters[(long long)smp * p.nsteps + n] = (su <= 1.7976931348623157e308) ? k : -1;
         }
     }
 }
@@ -443,12 +447,17 @@ extern "C" int bx_fom_picard_finemesh(int B, int N, int nsteps, const double *X,
     BX_REQUIRE(X && u0 && mu1 && mu2 && U && workspace, "null device pointer");
     FinePlan pl;
     fine_plan(N, pl);
-    int dev = 0, sms = 0, coop = 0, occ = 0;
-    BX_CUDA(cudaGetDevice(&dev));
-    BX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    BX_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
-    BX_CUDA(cudaFuncSetAttribute(fine_fom_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FINE_SMEM));
-    BX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fine_fom_kernel, FT, FINE_SMEM));
+    DeviceInfo di;
+    {
+        const int rcd = device_info(di);
+        if (rcd != BX_OK) return rcd;
+    }
+    const int sms = di.sms, coop = di.cooperative;
+    int occ = 0;
+    {
+        const int rco = kernel_occupancy(reinterpret_cast<const void *>(fine_fom_kernel), FT, FINE_SMEM, &occ);
+        if (rco != BX_OK) return rco;
+    }
     if (!coop || occ < 1 || pl.G > sms * occ || pl.G > FGMAX) {
         set_error("bx_fom_picard_finemesh: N = %d needs %d co-resident CTAs of %d nodes; this device runs %d", N, pl.G,
                   FNODES, (coop && occ >= 1) ? (sms * occ < FGMAX ? sms * occ : FGMAX) : 0);
@@ -460,7 +469,7 @@ extern "C" int bx_fom_picard_finemesh(int B, int N, int nsteps, const double *X,
     p.X = X; p.u0 = u0; p.u0_stride = u0_batched ? N : 0;
     p.mu1 = mu1; p.mu2 = mu2; p.At = At; p.E = E; p.tol2 = tol * tol;
     p.U = U; p.iters = iters;
-    p.bar = reinterpret_cast<unsigned int *>(ws);
+    p.bar = reinterpret_cast<unsigned long long *>(ws);
     p.g_h6 = reinterpret_cast<double *>(ws + pl.off_h6);
     p.g_hfs = reinterpret_cast<double *>(ws + pl.off_hfs);
     p.g_atf = reinterpret_cast<double *>(ws + pl.off_atf);

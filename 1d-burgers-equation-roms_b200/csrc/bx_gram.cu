@@ -199,9 +199,12 @@ __global__ void __launch_bounds__(256) gram_reduce_kernel(const GramParams p, in
 }
 
 static int gram_plan(int N, long long cols, GramParams &p, int &P) {
-    int dev = 0, sms = 0;
-    BX_CUDA(cudaGetDevice(&dev));
-    BX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    DeviceInfo di;
+    {
+        const int rcd = device_info(di);
+        if (rcd != BX_OK) return rcd;
+    }
+    const int sms = di.sms;
     p.N = N; p.cols = cols;
     p.nb = (N + GT - 1) / GT;
     p.T = p.nb * (p.nb + 1) / 2;
@@ -242,7 +245,10 @@ extern "C" int bx_gram_accumulate(int N, long long cols, const double *S, double
     if (rc != BX_OK) return rc;
     p.S = S; p.G = G; p.part = static_cast<double *>(workspace); p.accumulate = accumulate ? 1 : 0;
     p.bulk_ok = ((N & 1) == 0) && ((reinterpret_cast<uintptr_t>(S) & 15u) == 0);
-    BX_CUDA(cudaFuncSetAttribute(gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G_SMEM));
+    {
+        const int rco = kernel_occupancy(reinterpret_cast<const void *>(gram_kernel), GTHREADS, G_SMEM, nullptr);
+        if (rco != BX_OK) return rco;
+    }
     gram_kernel<<<P, GTHREADS, G_SMEM, st>>>(p);
     BX_LAUNCH_CHECK();
     gram_reduce_kernel<<<dim3(GT * GT / 256, p.T), 256, 0, st>>>(p, P);

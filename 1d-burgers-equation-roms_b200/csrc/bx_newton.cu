@@ -263,7 +263,17 @@ __global__ void __launch_bounds__(WARPS * 32, 1) fom_newton_kernel(const NewtonP
             double *Un1 = Us + (long long)(n + 1) * N;
 #pragma unroll
             for (int j = 0; j < M; ++j) if (node0 + j < N) Un1[j] = u[j];
-            if (lane == 0 && p.iters) p.iters[(long long)s * p.nsteps + n] = k;
+            const bool finite = su <= 1.7976931348623157e308;   // false for inf and NaN
+            if (lane == 0 && p.iters) p.iters[(long long)s * p.nsteps + n] = finite ? k : -1;
+            if (!finite) {   // flag -1 and NaN snapshots from here on; the batch goes on (include/burgers_b200.h)
+                const double qnan = __longlong_as_double(0x7ff8000000000000ll);
+                for (++n; n < p.nsteps; ++n) {
+                    double *Un2 = Us + (long long)(n + 1) * N;
+#pragma unroll
+                    for (int j = 0; j < M; ++j) if (node0 + j < N) Un2[j] = qnan;
+                    if (lane == 0 && p.iters) p.iters[(long long)s * p.nsteps + n] = -1;
+                }
+            }
         }
     }
 }
@@ -273,13 +283,14 @@ static int launch_newton(const NewtonParams &p, cudaStream_t st) {
     using L = NewtonSmem<M>;
     const size_t smem = L::bytes(WARPS);
     auto kern = fom_newton_kernel<M, WARPS>;
-    BX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int dev = 0, sms = 0, occ = 0;
-    BX_CUDA(cudaGetDevice(&dev));
-    BX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    BX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, WARPS * 32, smem));
+    DeviceInfo di;
+    int rc = device_info(di);
+    if (rc != BX_OK) return rc;
+    int occ = 0;
+    rc = kernel_occupancy(reinterpret_cast<const void *>(kern), WARPS * 32, smem, &occ);
+    if (rc != BX_OK) return rc;
     BX_REQUIRE(occ >= 1, "newton kernel does not fit on an SM (smem %zu B)", smem);
-    long long ctas = (long long)sms * occ;
+    long long ctas = (long long)di.sms * occ;
     const long long need = ((long long)p.B + WARPS - 1) / WARPS;
     if (ctas > need) ctas = need;
     BX_CUDA(cudaMemsetAsync(p.counter, 0, sizeof(unsigned int), st));
@@ -304,7 +315,7 @@ extern "C" int bx_fom_newton_trajectories(int B, int N, int nsteps, const double
     p.B = B; p.N = N; p.nsteps = nsteps; p.kmax = kmax;
     p.X = X; p.u0 = u0; p.u0_stride = u0_batched ? N : 0;
     p.mu1 = mu1; p.mu2 = mu2; p.At = At; p.E = E; p.lambda = lambda; p.tol2 = tol * tol;
-    p.U = U; p.iters = iters; p.counter = static_cast<unsigned int *>(workspace);
+    p.U = U; p.iters = iters; p.counter = queue_slot(workspace);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (N <= 64) return launch_newton<2, 4>(p, st);
     if (N <= 128) return launch_newton<4, 4>(p, st);

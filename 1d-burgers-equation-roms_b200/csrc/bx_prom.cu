@@ -45,6 +45,7 @@ struct PromParams {
     double *hfs;         // workspace: (h/6)(f_gp1+f_gp2) (B, N), element e at [e]
     double *U;
     int *iters;
+    double *err_hist;    // optional (B, nsteps, kmax): |dq| / |q| after every iteration (:776)
     unsigned int *counter;
 };
 
@@ -112,7 +113,7 @@ int launch_prom_forcing(int B, int N, const double *X, const double *mu2, double
 // bx_prom_cta.cu: one CTA per trajectory, 32 <= n <= 240
 int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const double *u0, int u0_batched,
                     const double *mu1, const double *mu2, double At, double E, const double *Phi, int projection,
-                    double tol, int kmax, double *U, int *iters, void *workspace, long long mat_offset_bytes,
+                    double tol, int kmax, double *U, int *iters, double *err_hist, void *workspace, long long mat_offset_bytes,
                     cudaStream_t st, long long *mat_bytes_out);
 
 template <int NB, bool LSPG, bool PHIS>
@@ -227,6 +228,7 @@ __global__ void __launch_bounds__(PROM_MAXW * 32, 1) prom_kernel(const PromParam
             }
             __syncwarp();
             int k = 0;
+            bool finite = true;
             for (;;) {
                 // ================= phase B: assembly + contraction (:730-762) ============
                 double acc[TILES][2];
@@ -378,13 +380,23 @@ __global__ void __launch_bounds__(PROM_MAXW * 32, 1) prom_kernel(const PromParam
                     }
                 }
                 __syncwarp();
+                if (p.err_hist && lane == 0) p.err_hist[((long long)smp * p.nsteps + step) * p.kmax + k] = err;
                 ++k;
+                finite = (sd + sq) <= 1.7976931348623157e308;   // false for inf and NaN
                 if (!(err > p.tol) || k >= p.kmax) break;
             }
             // ---- snapshot step+1 (:783) and iteration count --------------------------------
             double *Un1 = Us + (long long)(step + 1) * N;
             for (int i = lane; i < N; i += 32) Un1[i] = w_u[sk(i, S, lgS)];
-            if (lane == 0 && p.iters) p.iters[(long long)smp * p.nsteps + step] = k;
+            if (lane == 0 && p.iters) p.iters[(long long)smp * p.nsteps + step] = finite ? k : -1;
+            if (!finite) {   // singular reduced system / overflow (np.linalg.LinAlgError at :767): flag -1 and NaN
+                const double qnan = __longlong_as_double(0x7ff8000000000000ll);   // snapshots from here on, batch goes on
+                for (++step; step < p.nsteps; ++step) {
+                    double *Un2 = Us + (long long)(step + 1) * N;
+                    for (int i = lane; i < N; i += 32) Un2[i] = qnan;
+                    if (lane == 0 && p.iters) p.iters[(long long)smp * p.nsteps + step] = -1;
+                }
+            }
         }
         __syncwarp();
     }
@@ -394,10 +406,12 @@ template <int NB, bool LSPG, bool PHIS>
 static int launch_prom_t(PromParams p, int min_warps, cudaStream_t st, bool *fits) {
     const PromGeom geo = PromGeom::make(p.N);
     const PromSmem lay = PromSmem::make(geo.NP, p.ldp, PHIS ? 1 : 0, NB * 8);
-    int dev = 0, sms = 0, maxsm = 0;
-    BX_CUDA(cudaGetDevice(&dev));
-    BX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    BX_CUDA(cudaDeviceGetAttribute(&maxsm, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+    DeviceInfo di;
+    {
+        const int rcd = device_info(di);
+        if (rcd != BX_OK) return rcd;
+    }
+    const int sms = di.sms, maxsm = di.max_smem_optin;
     const long long avail = (long long)maxsm / (long long)sizeof(double) - lay.per_cta;
     long long warps = avail > 0 ? avail / lay.per_warp : 0;
     if (warps > PROM_MAXW) warps = PROM_MAXW;
@@ -407,7 +421,10 @@ static int launch_prom_t(PromParams p, int min_warps, cudaStream_t st, bool *fit
     p.warps = (int)warps;
     const size_t smem = sizeof(double) * ((size_t)lay.per_cta + (size_t)warps * lay.per_warp);
     auto kern = prom_kernel<NB, LSPG, PHIS>;
-    BX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    {
+        const int rco = kernel_occupancy(reinterpret_cast<const void *>(kern), (int)warps * 32, smem, nullptr);
+        if (rco != BX_OK) return rco;
+    }
     long long ctas = sms;
     const long long need = ((long long)p.B + warps - 1) / warps;
     if (ctas > need) ctas = need;
@@ -456,7 +473,7 @@ extern "C" long long bx_prom_workspace_bytes(int B, int N, int n) {
         for (int pi = 0; pi < 2; ++pi) {
             long long m = 0;
             if (bx::launch_prom_cta(B, N, n, 0, nullptr, nullptr, 0, nullptr, nullptr, 0.0, 0.0, nullptr, projs[pi], 0.0, 1,
-                                    nullptr, nullptr, nullptr, 0, nullptr, &m) != BX_OK)
+                                    nullptr, nullptr, nullptr, nullptr, 0, nullptr, &m) != BX_OK)
                 return -1;
             if (m > mat) mat = m;
         }
@@ -467,7 +484,7 @@ extern "C" long long bx_prom_workspace_bytes(int B, int N, int n) {
 extern "C" int bx_prom_trajectories(int B, int N, int n, int nsteps, const double *X, const double *u0,
                                     int u0_batched, const double *mu1, const double *mu2, double At,
                                     double E, const double *Phi, int projection, double tol, int kmax,
-                                    double *U, int *iters, void *workspace, void *stream) {
+                                    double *U, int *iters, double *err_hist, void *workspace, void *stream) {
     using namespace bx;
     if (projection != BX_GALERKIN && projection != BX_LSPG) {
         set_error("Projection method '%d' is not available. Please use 'Galerkin' or 'LSPG'.", projection);
@@ -485,7 +502,7 @@ extern "C" int bx_prom_trajectories(int B, int N, int n, int nsteps, const doubl
             return BX_ERR_UNSUPPORTED;
         }
         return launch_prom_cta(B, N, n, nsteps, X, u0, u0_batched, mu1, mu2, At, E, Phi, projection, tol, kmax, U,
-                               iters, workspace, prom_forcing_bytes(B, N), static_cast<cudaStream_t>(stream), nullptr);
+                               iters, err_hist, workspace, prom_forcing_bytes(B, N), static_cast<cudaStream_t>(stream), nullptr);
     }
     PromParams p;
     p.B = B; p.N = N; p.n = n; p.nsteps = nsteps; p.kmax = kmax;
@@ -493,8 +510,8 @@ extern "C" int bx_prom_trajectories(int B, int N, int n, int nsteps, const doubl
     p.warps = 0;
     p.X = X; p.u0 = u0; p.u0_stride = u0_batched ? N : 0;
     p.mu1 = mu1; p.mu2 = mu2; p.At = At; p.E = E; p.tol = tol;
-    p.Phi = Phi; p.U = U; p.iters = iters;
-    p.counter = static_cast<unsigned int *>(workspace);
+    p.Phi = Phi; p.U = U; p.iters = iters; p.err_hist = err_hist;
+    p.counter = queue_slot(workspace);
     p.atf = reinterpret_cast<double *>(static_cast<char *>(workspace) + 256);
     p.hfs = p.atf + (size_t)B * N;
     cudaStream_t st = static_cast<cudaStream_t>(stream);

@@ -51,6 +51,7 @@ struct PromCtaParams {
     double *mat_ws;      // per-CTA reduced system when it does not fit in shared memory
     double *U;
     int *iters;
+    double *err_hist;   // optional (B, nsteps, kmax): |dq| / |q| after every iteration (:776)
     unsigned int *counter;
 };
 
@@ -227,6 +228,7 @@ __global__ void __launch_bounds__(UB <= 2 ? 256 : PC_MAXW * 32, UB <= 2 ? 3 : 1)
             }
             __syncthreads();
             int k = 0;
+            bool finite = true;
             for (;;) {
                 // ================= phase A: rows of A and R (:730-752) =========================
                 for (int i = tid; i < p.NPad; i += T) {
@@ -504,6 +506,7 @@ __global__ void __launch_bounds__(UB <= 2 ? 256 : PC_MAXW * 32, UB <= 2 ? 3 : 1)
                     double a = 0.0, b = 0.0;
                     for (int ww = 0; ww < W; ++ww) { a += s_red2[2 * ww]; b += s_red2[2 * ww + 1]; }
                     err = sqrt(a) / sqrt(b);
+                    finite = (a + b) <= 1.7976931348623157e308;   // false for inf and NaN
                 }
                 for (int i0 = warp * 8; i0 < N; i0 += W * 8) {
                     double v[8];
@@ -538,13 +541,22 @@ __global__ void __launch_bounds__(UB <= 2 ? 256 : PC_MAXW * 32, UB <= 2 ? 3 : 1)
                     if (t == 0 && i0 + g < N) s_u[sk(i0 + g, S, lgS)] = w1;
                 }
                 __syncthreads();
+                if (p.err_hist && tid == 0) p.err_hist[((long long)smp * p.nsteps + step) * p.kmax + k] = err;
                 ++k;
                 if (!(err > p.tol) || k >= p.kmax) break;
             }
             // ---- snapshot step+1 (:783) and iteration count ------------------------------------
             double *Un1 = Us + (long long)(step + 1) * N;
             for (int i = tid; i < N; i += T) Un1[i] = s_u[sk(i, S, lgS)];
-            if (tid == 0 && p.iters) p.iters[(long long)smp * p.nsteps + step] = k;
+            if (tid == 0 && p.iters) p.iters[(long long)smp * p.nsteps + step] = finite ? k : -1;
+            if (!finite) {   // singular reduced system / overflow (np.linalg.LinAlgError at :767): flag -1 and NaN
+                const double qnan = __longlong_as_double(0x7ff8000000000000ll);   // snapshots from here on, batch goes on
+                for (++step; step < p.nsteps; ++step) {
+                    double *Un2 = Us + (long long)(step + 1) * N;
+                    for (int i = tid; i < N; i += T) Un2[i] = qnan;
+                    if (tid == 0 && p.iters) p.iters[(long long)smp * p.nsteps + step] = -1;
+                }
+            }
         }
     }
 }
@@ -552,7 +564,7 @@ __global__ void __launch_bounds__(UB <= 2 ? 256 : PC_MAXW * 32, UB <= 2 ? 3 : 1)
 // ---- host: geometry, shared-memory fit, launch ----------------------------------------------------
 int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const double *u0, int u0_batched,
                     const double *mu1, const double *mu2, double At, double E, const double *Phi, int projection,
-                    double tol, int kmax, double *U, int *iters, void *workspace, long long mat_offset_bytes,
+                    double tol, int kmax, double *U, int *iters, double *err_hist, void *workspace, long long mat_offset_bytes,
                     cudaStream_t st, long long *mat_bytes_out) {
     PromCtaParams p;
     p.B = B; p.N = N; p.n = n; p.nsteps = nsteps; p.kmax = kmax;
@@ -569,19 +581,19 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
     int Wmin = 8;   // at least 8 warps: staging, the J pass and the lift are per-warp instruction bound
     while (Wmin < PC_MAXW && (Wmin * PC_UB < p.units || Wmin * 32 < p.NC)) Wmin *= 2;
     int force_w = 0, force_kc = 0;
-    if (const char *e = getenv("BX_PROM_CTA_TUNE")) {   // tuning aid: "W,KC" (e.g. 16,32); invalid values are ignored
-        int w = 0, kc = 0;
-        if (sscanf(e, "%d,%d", &w, &kc) == 2) {
-            if ((w == 8 || w == 16) && w >= Wmin) force_w = w;
-            if (kc == 8 || kc == 12 || kc == 16 || kc == 24 || kc == 32) force_kc = kc;
-        }
+    {   // explicit tuning knobs (bx_set_tuning); invalid values are ignored
+        const int w = tuning(BX_TUNE_PROM_CTA_WARPS), kc = tuning(BX_TUNE_PROM_CTA_CHUNK);
+        if ((w == 8 || w == 16) && w >= Wmin) force_w = w;
+        if (kc == 8 || kc == 12 || kc == 16 || kc == 24 || kc == 32) force_kc = kc;
     }
     p.lgS = 3;
     while ((1 << p.lgS) < N) ++p.lgS;
-    int dev = 0, sms = 0, maxsm = 0;
-    BX_CUDA(cudaGetDevice(&dev));
-    BX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    BX_CUDA(cudaDeviceGetAttribute(&maxsm, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+    DeviceInfo di;
+    {
+        const int rcd = device_info(di);
+        if (rcd != BX_OK) return rcd;
+    }
+    const int sms = di.sms, maxsm = di.max_smem_optin;
     static const int kcs[5] = {32, 24, 16, 12, 8};   // multiples of 4 (DMMA k-steps), <= 32 (workspace rows)
     const int NS = projection == BX_LSPG ? 2 : 3;
     PromCtaSmem lay;
@@ -643,8 +655,8 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
     }
     p.X = X; p.u0 = u0; p.u0_stride = u0_batched ? N : 0;
     p.mu1 = mu1; p.mu2 = mu2; p.At = At; p.E = E; p.tol = tol;
-    p.Phi = Phi; p.U = U; p.iters = iters;
-    p.counter = static_cast<unsigned int *>(workspace);
+    p.Phi = Phi; p.U = U; p.iters = iters; p.err_hist = err_hist;
+    p.counter = queue_slot(workspace);
     p.atf = reinterpret_cast<double *>(static_cast<char *>(workspace) + 256);
     p.hfs = p.atf + (size_t)B * N;
     p.Phip = reinterpret_cast<double *>(static_cast<char *>(workspace) + mat_offset_bytes);
@@ -655,8 +667,10 @@ int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const doub
         projection == BX_LSPG
             ? (UBsel == 1 ? prom_cta_kernel<true, 1> : UBsel == 2 ? prom_cta_kernel<true, 2> : prom_cta_kernel<true, PC_UB>)
             : (UBsel == 1 ? prom_cta_kernel<false, 1> : UBsel == 2 ? prom_cta_kernel<false, 2> : prom_cta_kernel<false, PC_UB>);
-    BX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    BX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, W * 32, smem));
+    {
+        const int rco = kernel_occupancy(reinterpret_cast<const void *>(kern), W * 32, smem, &occ);
+        if (rco != BX_OK) return rco;
+    }
     if (occ < 1) {
         set_error("bx_prom_trajectories: kernel does not fit on an SM (N = %d, n = %d)", N, n);
         return BX_ERR_UNSUPPORTED;

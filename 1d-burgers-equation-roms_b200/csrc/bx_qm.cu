@@ -28,7 +28,6 @@
 // A pre-kernel doubles the diagonal monomials of H once (Hp) and evaluates At F per sample.
 #include "bx_prom_common.cuh"
 #include <cstdint>
-#include <cstdlib>
 
 namespace bx {
 
@@ -46,6 +45,7 @@ struct QmParams {
     double *Tg;          // workspace: per warp slot (NP + 1) x 32 tangent rows (row 0 = zero row for node -1)
     double *U;
     int *iters;
+    double *err_hist;    // optional (B, nsteps, itmax): |dq| / max(1e-14, |q|) after every iteration (:1165)
     unsigned int *counter;
 };
 
@@ -301,6 +301,7 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel(const QmParams p) {
             }
         }
         __syncwarp();
+        bool bad = false;   // this warp's trajectory stopped being finite
 
         for (int step = 0; step < p.nsteps; ++step) {
             // ---- bn = M U^m + At F (:1140) and the initial guess q = Phi^T U^m (:1129) --------
@@ -319,14 +320,14 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel(const QmParams p) {
                     for (int r = 0; r < 4; ++r) q4[r] = fma(ph[(size_t)(i + r) * n], w_u[sk(i + r, S, lgS)], q4[r]);
                 }
                 for (; i < N; ++i) q4[0] = fma(ph[(size_t)i * n], w_u[sk(i, S, lgS)], q4[0]);
-                q = (active && lane < n) ? (q4[0] + q4[1]) + (q4[2] + q4[3]) : 0.0;
+                q = (active && !bad && lane < n) ? (q4[0] + q4[1]) + (q4[2] + q4[3]) : 0.0;
             }
             __syncwarp();
             w_q[lane] = q;
             tangent_pass();   // u = decoder(q) (:1130), T(q)
 
             int it_done = 0;
-            bool done = !active;
+            bool done = !active || bad;
             for (int it = 0; it < p.itmax; ++it) {
               if (!done) {
                 // ================= contraction (:1134-1156) ==================================
@@ -413,6 +414,8 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel(const QmParams p) {
                 const double sd = warp_sum((lane < n) ? dq * dq : 0.0);
                 const double sq = warp_sum(q * q);
                 const double rel = sqrt(sd) / fmax(1e-14, sqrt(sq));
+                if (p.err_hist && lane == 0) p.err_hist[((long long)smp * p.nsteps + step) * p.itmax + it] = rel;
+                if (!((sd + sq) <= 1.7976931348623157e308)) { bad = true; done = true; q = 0.0; }   // inf / NaN
                 __syncwarp();
                 w_q[lane] = q;
                 if (lane == 0) { w_u[sk(-1, S, lgS)] = 0.0; w_u[sk(NP, S, lgS)] = 0.0; }   // halo words the matrix overwrote
@@ -425,8 +428,11 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel(const QmParams p) {
             }
             if (active) {
                 double *Un1 = Us + (long long)(step + 1) * N;
-                for (int i = lane; i < N; i += 32) Un1[i] = w_u[sk(i, S, lgS)];
-                if (lane == 0 && p.iters) p.iters[(long long)smp * p.nsteps + step] = it_done;
+                // a trajectory whose reduced system went singular / overflowed (np.linalg.LinAlgError at :1161) carries
+                // the flag -1 and NaN snapshots from that step on; the other seven of the group are unaffected
+                const double qnan = __longlong_as_double(0x7ff8000000000000ll);
+                for (int i = lane; i < N; i += 32) Un1[i] = bad ? qnan : w_u[sk(i, S, lgS)];
+                if (lane == 0 && p.iters) p.iters[(long long)smp * p.nsteps + step] = bad ? -1 : it_done;
             }
         }
     }
@@ -610,6 +616,7 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel_ts(const QmParams p
             }
         }
         __syncwarp();
+        bool bad = false;   // this warp's trajectory stopped being finite
 
         for (int step = 0; step < p.nsteps; ++step) {
             for (int i = lane; i < N; i += 32) {
@@ -627,13 +634,13 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel_ts(const QmParams p
                     for (int r = 0; r < 4; ++r) q4[r] = fma(ph[(size_t)(i + r) * n], w_u[sk(i + r, S, lgS)], q4[r]);
                 }
                 for (; i < N; ++i) q4[0] = fma(ph[(size_t)i * n], w_u[sk(i, S, lgS)], q4[0]);
-                q = (active && lane < n) ? (q4[0] + q4[1]) + (q4[2] + q4[3]) : 0.0;
+                q = (active && !bad && lane < n) ? (q4[0] + q4[1]) + (q4[2] + q4[3]) : 0.0;
             }
             __syncwarp();
             w_q[lane] = q;
 
             int it_done = 0;
-            bool done = !active;
+            bool done = !active || bad;
             for (int it = 0; it < p.itmax; ++it) {
                 // ---- prologue: run-boundary rows (global scratch) and chunk 0 ----------------------------
                 __syncthreads();   // every q published; previous contraction / solve finished
@@ -748,6 +755,8 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel_ts(const QmParams p
                     const double sd = warp_sum((lane < n) ? dq * dq : 0.0);
                     const double sq = warp_sum(q * q);
                     const double rel = sqrt(sd) / fmax(1e-14, sqrt(sq));
+                    if (p.err_hist && lane == 0) p.err_hist[((long long)smp * p.nsteps + step) * p.itmax + it] = rel;
+                    if (!((sd + sq) <= 1.7976931348623157e308)) { bad = true; done = true; q = 0.0; }   // inf / NaN
                     __syncwarp();
                     w_q[lane] = q;
                     if (lane == 0) { w_u[sk(-1, S, lgS)] = 0.0; w_u[sk(NP, S, lgS)] = 0.0; }
@@ -769,22 +778,29 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel_ts(const QmParams p
             __syncthreads();
             if (active) {
                 double *Un1 = Us + (long long)(step + 1) * N;
-                for (int i = lane; i < N; i += 32) Un1[i] = w_u[sk(i, S, lgS)];
-                if (lane == 0 && p.iters) p.iters[(long long)smp * p.nsteps + step] = it_done;
+                // a trajectory whose reduced system went singular / overflowed (np.linalg.LinAlgError at :1161) carries
+                // the flag -1 and NaN snapshots from that step on; the other seven of the group are unaffected
+                const double qnan = __longlong_as_double(0x7ff8000000000000ll);
+                for (int i = lane; i < N; i += 32) Un1[i] = bad ? qnan : w_u[sk(i, S, lgS)];
+                if (lane == 0 && p.iters) p.iters[(long long)smp * p.nsteps + step] = bad ? -1 : it_done;
             }
         }
     }
 }
 
 struct QmPlan {
-    int sms, NP, NB;
+    int sms, maxsm, NP, NB;
     size_t off_hs, off_atf, off_tg, total;
 };
 
 static int qm_plan(int B, int N, int n, QmPlan &pl) {
-    int dev = 0;
-    BX_CUDA(cudaGetDevice(&dev));
-    BX_CUDA(cudaDeviceGetAttribute(&pl.sms, cudaDevAttrMultiProcessorCount, dev));
+    DeviceInfo di;
+    {
+        const int rcd = device_info(di);
+        if (rcd != BX_OK) return rcd;
+    }
+    pl.sms = di.sms;
+    pl.maxsm = di.max_smem_optin;
     const PromGeom geo = PromGeom::make(N);
     pl.NP = geo.NP;
     pl.NB = n / 8 + 1;   // 8 NB > n: column n of the contraction carries R
@@ -799,9 +815,7 @@ static int qm_plan(int B, int N, int n, QmPlan &pl) {
 template <int NB, bool LSPG>
 static int launch_qm_t(QmParams p, const QmPlan &pl, const double *H, cudaStream_t st) {
     const QmSmem lay = QmSmem::make(pl.NP);
-    int dev = 0, maxsm = 0;
-    BX_CUDA(cudaGetDevice(&dev));
-    BX_CUDA(cudaDeviceGetAttribute(&maxsm, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+    const int maxsm = pl.maxsm;
     const long long warps = QM_MAXW;   // eight trajectories per CTA in lock step (the M of the tangent DMMA)
     if ((long long)sizeof(double) * (lay.per_cta + warps * lay.per_warp) > (long long)maxsm) {
         set_error("bx_qm_prom_trajectories: N = %d, n = %d does not fit in shared memory", p.N, p.n);
@@ -813,12 +827,13 @@ static int launch_qm_t(QmParams p, const QmPlan &pl, const double *H, cudaStream
     const QmTsSmem tl = QmTsSmem::make(lay);
     // v3 with the shared tile for NB <= QM_TS_MAX_NB (when it fits), else v2.  The chunked-global variant of v3 is kept
     // for A/B runs only: measured slower than v2 at n = 28 (4.8 / 5.1 vs 5.3 / 5.7 M it/s, profiles/r02n_qm_modes.txt).
-    // BX_QM_TS = 0 (v2) / 1 (shared tile) / 2 (chunked global) forces a choice.
+    // bx_set_tuning(BX_TUNE_QM_SCHEDULE, 0 (v2) / 1 (shared tile) / 2 (chunked global)) forces a choice.
     int mode = (sizeof(double) * (size_t)tl.total <= (size_t)maxsm && NB <= QM_TS_MAX_NB) ? 1 : 0;
-    if (const char *e = getenv("BX_QM_TS")) {
-        if (e[0] == '0') mode = 0;
-        if (e[0] == '1' && sizeof(double) * (size_t)tl.total <= (size_t)maxsm) mode = 1;
-        if (e[0] == '2') mode = 2;
+    {
+        const int f = tuning(BX_TUNE_QM_SCHEDULE);
+        if (f == 0) mode = 0;
+        if (f == 1 && sizeof(double) * (size_t)tl.total <= (size_t)maxsm) mode = 1;
+        if (f == 2) mode = 2;
     }
     if (mode == 1) {
         kern = qm_kernel_ts<NB, LSPG, 0>;
@@ -826,7 +841,10 @@ static int launch_qm_t(QmParams p, const QmPlan &pl, const double *H, cudaStream
     } else if (mode == 2) {
         kern = qm_kernel_ts<NB, LSPG, 2>;
     }
-    BX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    {
+        const int rco = kernel_occupancy(reinterpret_cast<const void *>(kern), (int)warps * 32, smem, nullptr);
+        if (rco != BX_OK) return rco;
+    }
     long long ctas = pl.sms;
     const long long need = ((long long)p.B + warps - 1) / warps;
     if (ctas > need) ctas = need;
@@ -852,6 +870,17 @@ static int launch_qm(const QmParams &p, const QmPlan &pl, const double *H, cudaS
 
 }  // namespace bx
 
+extern "C" int bx_qm_schedule_available(int N, int n, int schedule) {
+    using namespace bx;
+    if (N < 2 || n < 1 || n > 31) return 0;
+    if (schedule == 0 || schedule == 2) return 1;
+    if (schedule != 1) return 0;
+    QmPlan pl;
+    if (qm_plan(1, N, n, pl) != BX_OK) return 0;
+    const QmTsSmem tl = QmTsSmem::make(QmSmem::make(pl.NP));
+    return sizeof(double) * (size_t)tl.total <= (size_t)pl.maxsm ? 1 : 0;
+}
+
 extern "C" long long bx_qm_workspace_bytes(int B, int N, int n) {
     using namespace bx;
     if (B < 0 || N < 2 || n < 1) return -1;
@@ -863,7 +892,7 @@ extern "C" long long bx_qm_workspace_bytes(int B, int N, int n) {
 extern "C" int bx_qm_prom_trajectories(int B, int N, int n, int nsteps, const double *X, const double *u0,
                                        int u0_batched, const double *uxa, const double *mu2, double At, double E,
                                        const double *Phi, const double *H, int projection, double tol, int itmax,
-                                       double *U, int *iters, void *workspace, void *stream) {
+                                       double *U, int *iters, double *err_hist, void *workspace, void *stream) {
     using namespace bx;
     if (projection != BX_GALERKIN && projection != BX_LSPG) {
         set_error("projection must be 'Galerkin' or 'LSPG'");
@@ -885,11 +914,11 @@ extern "C" int bx_qm_prom_trajectories(int B, int N, int n, int nsteps, const do
     p.X = X; p.u0 = u0; p.u0_stride = u0_batched ? N : 0;
     p.mu1 = uxa; p.mu2 = mu2; p.At = At; p.E = E; p.tol = tol;
     p.Phi = Phi;
-    p.counter = reinterpret_cast<unsigned int *>(ws);
+    p.counter = queue_slot(ws);
     p.Hs = reinterpret_cast<double *>(ws + pl.off_hs);
     p.atf = reinterpret_cast<double *>(ws + pl.off_atf);
     p.Tg = reinterpret_cast<double *>(ws + pl.off_tg);
-    p.U = U; p.iters = iters;
+    p.U = U; p.iters = iters; p.err_hist = err_hist;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     return projection == BX_LSPG ? launch_qm<true>(p, pl, H, st) : launch_qm<false>(p, pl, H, st);
 }

@@ -113,7 +113,10 @@ static int launch_solve(int B, int N, const double *dl, const double *d, const d
     constexpr int WARPS = 4;
     const size_t smem = sizeof(double) * WARPS * 4 * 32 * (M + 1);
     auto kern = tridiag_solve_update_kernel<M, WARPS>;
-    BX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    {
+        const int rco = kernel_occupancy(reinterpret_cast<const void *>(kern), WARPS * 32, smem, nullptr);
+        if (rco != BX_OK) return rco;
+    }
     kern<<<(B + WARPS - 1) / WARPS, WARPS * 32, smem, st>>>(B, N, dl, d, du, R, Uk, Uk1, err);
     BX_LAUNCH_CHECK();
     return BX_OK;

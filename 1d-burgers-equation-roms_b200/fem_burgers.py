@@ -26,8 +26,16 @@ def _ptr(t):
     return None if t is None else t.data_ptr()
 
 
-def _stream():
-    return torch.cuda.current_stream().cuda_stream
+def _on_device(method):
+    """Run a FEMBurgers method with the object's device current: the C library enqueues on the stream it is
+    given and queries the *current* device, so an object built for cuda:1 must not run while cuda:0 is current."""
+    import functools
+
+    @functools.wraps(method)
+    def wrapper(self, *args, **kwargs):
+        with torch.cuda.device(self.device):
+            return method(self, *args, **kwargs)
+    return wrapper
 
 
 def validate_mesh(X, T):
@@ -63,8 +71,10 @@ class FEMBurgers:
         self.n_nodes = int(self.X.size)
         self._device = device
         self._Xd = None
-        self._ws = None
+        self._ws = {}       # per-stream work-queue workspaces: launches on different streams never share one
+        self._big_ws = {}   # per-stream grow-only scratch
         self.last_iters = None  # per-step nonlinear iteration counts of the last legacy call
+        self.verbose = False    # True: the legacy single-sample methods print the reference's progress lines
 
     # ------------------------------------------------------------------ device plumbing
     @property
@@ -81,16 +91,25 @@ class FEMBurgers:
             self._Xd = torch.from_numpy(self.X).to(self.device)
         return self._Xd
 
+    def _stream(self):
+        return torch.cuda.current_stream(self.device).cuda_stream
+
     def _workspace(self):
-        if self._ws is None:
-            self._ws = torch.zeros(int(_lib.load().bx_workspace_bytes()), dtype=torch.uint8, device=self.device)
-        return self._ws
+        key = self._stream()
+        ws = self._ws.get(key)
+        if ws is None:
+            ws = self._ws[key] = torch.zeros(int(_lib.load().bx_workspace_bytes()), dtype=torch.uint8,
+                                             device=self.device)
+        return ws
 
     def _scratch(self, nbytes):
-        """Grow-only device scratch for the entry points whose workspace depends on the batch size."""
-        if getattr(self, "_big_ws", None) is None or self._big_ws.numel() < nbytes:
-            self._big_ws = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
-        return self._big_ws
+        """Grow-only device scratch for the entry points whose workspace depends on the batch size; one per
+        stream, because a workspace must not be shared by launches that may overlap (include/burgers_b200.h)."""
+        key = self._stream()
+        ws = self._big_ws.get(key)
+        if ws is None or ws.numel() < nbytes:
+            ws = self._big_ws[key] = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
+        return ws
 
     def _dev(self, a, shape=None):
         """numpy / scalar / tensor -> contiguous float64 CUDA tensor."""
@@ -106,48 +125,54 @@ class FEMBurgers:
         return torch.empty(shape, dtype=dtype, device=self.device)
 
     # ------------------------------------------------------------------ batched operators
+    @_on_device
     def mass_bands(self):
         """(dl, d, du) of M, each (N,) — compute_mass_matrix, FEM/fem_burgers.py:324."""
         N = self.n_nodes
         dl, d, du = self._new(N), self._new(N), self._new(N)
         lib = _lib.load()
-        _lib.check(lib.bx_mass_bands(N, _ptr(self.Xd), _ptr(dl), _ptr(d), _ptr(du), _stream()), "bx_mass_bands")
+        _lib.check(lib.bx_mass_bands(N, _ptr(self.Xd), _ptr(dl), _ptr(d), _ptr(du), self._stream()), "bx_mass_bands")
         return dl, d, du
 
+    @_on_device
     def diffusion_bands(self):
         N = self.n_nodes
         dl, d, du = self._new(N), self._new(N), self._new(N)
         lib = _lib.load()
-        _lib.check(lib.bx_diffusion_bands(N, _ptr(self.Xd), _ptr(dl), _ptr(d), _ptr(du), _stream()),
+        _lib.check(lib.bx_diffusion_bands(N, _ptr(self.Xd), _ptr(dl), _ptr(d), _ptr(du), self._stream()),
                    "bx_diffusion_bands")
         return dl, d, du
 
+    @_on_device
     def convection_bands(self, U):
         """U (B, N) -> (dl, d, du) each (B, N) — compute_convection_matrix, :389."""
         U = self._dev(U).reshape(-1, self.n_nodes)
         B, N = U.shape
         dl, d, du = self._new(B, N), self._new(B, N), self._new(B, N)
         lib = _lib.load()
-        _lib.check(lib.bx_convection_bands(B, N, _ptr(self.Xd), _ptr(U), _ptr(dl), _ptr(d), _ptr(du), _stream()),
+        _lib.check(lib.bx_convection_bands(B, N, _ptr(self.Xd), _ptr(U), _ptr(dl), _ptr(d), _ptr(du), self._stream()),
                    "bx_convection_bands")
         return dl, d, du
 
+    @_on_device
     def convection_derivative_bands(self):
         N = self.n_nodes
         dl, d, du = self._new(N), self._new(N), self._new(N)
         lib = _lib.load()
-        _lib.check(lib.bx_convection_derivative_bands(N, _ptr(self.Xd), _ptr(dl), _ptr(d), _ptr(du), _stream()),
+        _lib.check(lib.bx_convection_derivative_bands(N, _ptr(self.Xd), _ptr(dl), _ptr(d), _ptr(du), self._stream()),
                    "bx_convection_derivative_bands")
         return dl, d, du
 
+    @_on_device
     def forcing_vector_batch(self, mu2):
         mu2 = self._dev(mu2).reshape(-1)
         B, N = mu2.numel(), self.n_nodes
         F = self._new(B, N)
         lib = _lib.load()
-        _lib.check(lib.bx_forcing_vector(B, N, _ptr(self.Xd), _ptr(mu2), _ptr(F), _stream()), "bx_forcing_vector")
+        _lib.check(lib.bx_forcing_vector(B, N, _ptr(self.Xd), _ptr(mu2), _ptr(F), self._stream()), "bx_forcing_vector")
         return F
 
+    @_on_device
     def supg_term_batch(self, U, mu2):
         U = self._dev(U).reshape(-1, self.n_nodes)
         mu2 = self._dev(mu2).reshape(-1)
@@ -156,9 +181,10 @@ class FEMBurgers:
             raise ValueError("mu2 must have one entry per state")
         S = self._new(B, N)
         lib = _lib.load()
-        _lib.check(lib.bx_supg_term(B, N, _ptr(self.Xd), _ptr(U), _ptr(mu2), _ptr(S), _stream()), "bx_supg_term")
+        _lib.check(lib.bx_supg_term(B, N, _ptr(self.Xd), _ptr(U), _ptr(mu2), _ptr(S), self._stream()), "bx_supg_term")
         return S
 
+    @_on_device
     def assemble_picard(self, Uk, Un, mu1, mu2, At, E=0.0, supg=True, want_b=True):
         """One Picard linearisation for B states (FEM/fem_burgers.py:667-689).
         Returns dl, d, du, b, R — all (B, N) CUDA tensors (b is None when want_b=False)."""
@@ -174,9 +200,10 @@ class FEMBurgers:
         lib = _lib.load()
         _lib.check(lib.bx_assemble_picard(B, N, _ptr(self.Xd), _ptr(Uk), _ptr(Un), _ptr(mu1), _ptr(mu2),
                                           float(At), float(E), int(bool(supg)), _ptr(dl), _ptr(d), _ptr(du),
-                                          _ptr(b), _ptr(R), _stream()), "bx_assemble_picard")
+                                          _ptr(b), _ptr(R), self._stream()), "bx_assemble_picard")
         return dl, d, du, b, R
 
+    @_on_device
     def tridiag_solve_update(self, dl, d, du, R, Uk, out=None):
         """delta = A^-1(-R); U1 = Uk + delta; err = |delta|/|U1| (FEM/fem_burgers.py:692-698)."""
         Uk = self._dev(Uk).reshape(-1, self.n_nodes)
@@ -185,14 +212,12 @@ class FEMBurgers:
         err = self._new(B)
         lib = _lib.load()
         _lib.check(lib.bx_tridiag_solve_update(B, N, _ptr(dl), _ptr(d), _ptr(du), _ptr(R), _ptr(Uk), _ptr(U1),
-                                               _ptr(err), _stream()), "bx_tridiag_solve_update")
+                                               _ptr(err), self._stream()), "bx_tridiag_solve_update")
         return U1, err
 
     # ------------------------------------------------------------------ batched trajectories
-    def fom_burgers_batch(self, At, nTimeSteps, u0, mu1, E, mu2, out=None, iters_out=None,
-                          tol=1e-6, kmax=20):
-        """fom_burgers (FEM/fem_burgers.py:646) for B samples: mu1, mu2 (B,).
-        Returns U (B, nTimeSteps+1, N) and iters (B, nTimeSteps) int32, CUDA tensors."""
+    def _sweep_args(self, u0, mu1, mu2, nTimeSteps, out, iters_out):
+        """Common argument handling and validation of the trajectory entry points."""
         mu1 = self._dev(mu1).reshape(-1)
         mu2 = self._dev(mu2).reshape(-1)
         B, N = mu1.numel(), self.n_nodes
@@ -207,46 +232,51 @@ class FEMBurgers:
             raise ValueError("u0 must have shape (N,) or (B, N)")
         nT = int(nTimeSteps)
         U = out if out is not None else self._new(B, nT + 1, N)
-        if tuple(U.shape) != (B, nT + 1, N) or U.dtype != torch.float64 or not U.is_contiguous():
-            raise ValueError("out must be a contiguous float64 tensor of shape (B, nTimeSteps+1, N)")
+        if not isinstance(U, torch.Tensor) or tuple(U.shape) != (B, nT + 1, N) or U.dtype != torch.float64 \
+                or not U.is_contiguous() or U.device != self.device:
+            raise ValueError(f"out must be a contiguous float64 tensor of shape (B, nTimeSteps+1, N) on {self.device}")
         iters = iters_out if iters_out is not None else self._new(B, nT, dtype=torch.int32)
+        if not isinstance(iters, torch.Tensor) or tuple(iters.shape) != (B, nT) or iters.dtype != torch.int32 \
+                or not iters.is_contiguous() or iters.device != self.device:
+            raise ValueError(f"iters_out must be a contiguous int32 tensor of shape (B, nTimeSteps) on {self.device}")
+        return mu1, mu2, u0, batched, B, N, nT, U, iters
+
+    def _err_hist(self, err_hist, B, nT, kmax):
+        if err_hist is None:
+            return None
+        if not isinstance(err_hist, torch.Tensor) or tuple(err_hist.shape) != (B, nT, int(kmax)) \
+                or err_hist.dtype != torch.float64 or not err_hist.is_contiguous() or err_hist.device != self.device:
+            raise ValueError(f"err_hist must be a contiguous float64 tensor (B, nTimeSteps, kmax) on {self.device}")
+        return err_hist
+
+    @_on_device
+    def fom_burgers_batch(self, At, nTimeSteps, u0, mu1, E, mu2, out=None, iters_out=None,
+                          tol=1e-6, kmax=20, err_hist=None):
+        """fom_burgers (FEM/fem_burgers.py:646) for B samples: mu1, mu2 (B,).
+        Returns U (B, nTimeSteps+1, N) and iters (B, nTimeSteps) int32, CUDA tensors.  iters[b, step] = -1 (and NaN
+        snapshots) from the first step of sample b whose state is not finite.  err_hist: optional preallocated
+        (B, nTimeSteps, kmax) float64 tensor that receives |delta_U| / |U1| of every executed iteration (:698)."""
+        mu1, mu2, u0, batched, B, N, nT, U, iters = self._sweep_args(u0, mu1, mu2, nTimeSteps, out, iters_out)
+        eh = self._err_hist(err_hist, B, nT, kmax)
         lib = _lib.load()
         if B == 0:
             return U, iters
         if N > self.WARP_MESH_MAX:
+            if eh is not None:
+                raise ValueError("err_hist is not available on the fine-mesh path (N > 1024)")
             # fine mesh (BASELINE config 5): persistent cooperative kernel, partition solve across CTAs
             ws = self._scratch(int(lib.bx_fine_workspace_bytes(N)))
             _lib.check(lib.bx_fom_picard_finemesh(B, N, nT, _ptr(self.Xd), _ptr(u0), batched, _ptr(mu1),
                                                   _ptr(mu2), float(At), float(E), float(tol), int(kmax),
-                                                  _ptr(U), _ptr(iters), _ptr(ws), _stream()),
+                                                  _ptr(U), _ptr(iters), _ptr(ws), self._stream()),
                        "bx_fom_picard_finemesh")
             return U, iters
         _lib.check(lib.bx_fom_picard_trajectories(B, N, nT, _ptr(self.Xd), _ptr(u0), batched, _ptr(mu1),
                                                   _ptr(mu2), float(At), float(E), float(tol), int(kmax),
-                                                  _ptr(U), _ptr(iters), _ptr(self._workspace()), _stream()),
+                                                  _ptr(U), _ptr(iters), _ptr(eh), _ptr(self._workspace()),
+                                                  self._stream()),
                    "bx_fom_picard_trajectories")
         return U, iters
-
-    def _sweep_args(self, u0, mu1, mu2, nTimeSteps, out, iters_out):
-        """Common argument handling of the trajectory entry points."""
-        mu1 = self._dev(mu1).reshape(-1)
-        mu2 = self._dev(mu2).reshape(-1)
-        B, N = mu1.numel(), self.n_nodes
-        if mu2.numel() != B:
-            raise ValueError("mu1 and mu2 must have the same number of samples")
-        u0 = self._dev(u0)
-        if u0.numel() == N:
-            batched = 0
-        elif u0.numel() == B * N:
-            batched = 1
-        else:
-            raise ValueError("u0 must have shape (N,) or (B, N)")
-        nT = int(nTimeSteps)
-        U = out if out is not None else self._new(B, nT + 1, N)
-        if tuple(U.shape) != (B, nT + 1, N) or U.dtype != torch.float64 or not U.is_contiguous():
-            raise ValueError("out must be a contiguous float64 tensor of shape (B, nTimeSteps+1, N)")
-        iters = iters_out if iters_out is not None else self._new(B, nT, dtype=torch.int32)
-        return mu1, mu2, u0, batched, B, N, nT, U, iters
 
     @staticmethod
     def _projection_code(projection):
@@ -257,6 +287,7 @@ class FEMBurgers:
             return _lib.BX_LSPG
         raise ValueError(f"Projection method '{projection}' is not available. Please use 'Galerkin' or 'LSPG'.")
 
+    @_on_device
     def fom_burgers_newton_batch(self, At, nTimeSteps, u0, mu1, E, mu2, out=None, iters_out=None,
                                  lambda_=0.1, tol=1e-6, kmax=100):
         """fom_burgers_newton as coded (FEM/fem_burgers.py:584) for B samples.
@@ -268,15 +299,18 @@ class FEMBurgers:
         _lib.check(lib.bx_fom_newton_trajectories(B, N, nT, _ptr(self.Xd), _ptr(u0), batched, _ptr(mu1),
                                                   _ptr(mu2), float(At), float(E), float(lambda_), float(tol),
                                                   int(kmax), _ptr(U), _ptr(iters), _ptr(self._workspace()),
-                                                  _stream()), "bx_fom_newton_trajectories")
+                                                  self._stream()), "bx_fom_newton_trajectories")
         return U, iters
 
+    @_on_device
     def pod_prom_burgers_batch(self, At, nTimeSteps, u0, mu1, E, mu2, Phi, projection="Galerkin", out=None,
-                               iters_out=None, tol=1e-6, kmax=20):
+                               iters_out=None, tol=1e-6, kmax=20, err_hist=None):
         """pod_prom_burgers (FEM/fem_burgers.py:709) for B samples: mu1, mu2 (B,), Phi (N, n) shared.
-        Returns U (B, nTimeSteps+1, N) and iters (B, nTimeSteps) int32, CUDA tensors."""
+        Returns U (B, nTimeSteps+1, N) and iters (B, nTimeSteps) int32, CUDA tensors; iters = -1 flags a sample
+        whose reduced system went singular / non-finite (the reference raises LinAlgError at :767)."""
         code = self._projection_code(projection)
         mu1, mu2, u0, batched, B, N, nT, U, iters = self._sweep_args(u0, mu1, mu2, nTimeSteps, out, iters_out)
+        eh = self._err_hist(err_hist, B, nT, kmax)
         Phi = self._dev(Phi)
         if Phi.dim() != 2 or Phi.shape[0] != N:
             raise ValueError("Phi must have shape (N, n)")
@@ -289,12 +323,14 @@ class FEMBurgers:
             raise _lib.BurgersB200Error("bx_prom_workspace_bytes failed: " + lib.bx_last_error().decode())
         _lib.check(lib.bx_prom_trajectories(B, N, n, nT, _ptr(self.Xd), _ptr(u0), batched, _ptr(mu1), _ptr(mu2),
                                             float(At), float(E), _ptr(Phi), code, float(tol), int(kmax),
-                                            _ptr(U), _ptr(iters), _ptr(self._scratch(need)), _stream()),
+                                            _ptr(U), _ptr(iters), _ptr(eh), _ptr(self._scratch(need)),
+                                            self._stream()),
                    "bx_prom_trajectories")
         return U, iters
 
+    @_on_device
     def pod_quadratic_manifold_batch(self, At, nTimeSteps, u0, uxa, E, mu2, Phi, H, projection="LSPG", out=None,
-                                     iters_out=None, newton_tol=1e-6, newton_itmax=25):
+                                     iters_out=None, newton_tol=1e-6, newton_itmax=25, err_hist=None):
         """pod_quadratic_manifold (FEM/fem_burgers.py:1081) for B samples: uxa, mu2 (B,), Phi (N, n) and
         H (N, n(n+1)/2) shared.  Returns U (B, nTimeSteps+1, N) and iters (B, nTimeSteps) int32, CUDA tensors."""
         pl = str(projection).lower()   # the reference compares projection.lower() (:1150-1158)
@@ -305,6 +341,7 @@ class FEMBurgers:
         else:
             raise ValueError("projection must be 'Galerkin' or 'LSPG'")
         uxa, mu2, u0, batched, B, N, nT, U, iters = self._sweep_args(u0, uxa, mu2, nTimeSteps, out, iters_out)
+        eh = self._err_hist(err_hist, B, nT, newton_itmax)
         Phi = self._dev(Phi)
         H = self._dev(H)
         if Phi.dim() != 2 or Phi.shape[0] != N:
@@ -320,8 +357,9 @@ class FEMBurgers:
             raise _lib.BurgersB200Error("bx_qm_workspace_bytes failed: " + lib.bx_last_error().decode())
         _lib.check(lib.bx_qm_prom_trajectories(B, N, n, nT, _ptr(self.Xd), _ptr(u0), batched, _ptr(uxa), _ptr(mu2),
                                                float(At), float(E), _ptr(Phi), _ptr(H), code, float(newton_tol),
-                                               int(newton_itmax), _ptr(U), _ptr(iters), _ptr(self._scratch(need)),
-                                               _stream()), "bx_qm_prom_trajectories")
+                                               int(newton_itmax), _ptr(U), _ptr(iters), _ptr(eh),
+                                               _ptr(self._scratch(need)), self._stream()),
+                   "bx_qm_prom_trajectories")
         return U, iters
 
     # ------------------------------------------------------------------ legacy surface (numpy / scipy in-out)
@@ -349,36 +387,83 @@ class FEMBurgers:
         return self.supg_term_batch(np.asarray(U_n, dtype=np.float64).reshape(1, -1), [float(mu2)]) \
             .reshape(-1).cpu().numpy()
 
+    # -- single-sample trajectories: the reference's signatures and return type, ndarray (N, nTimeSteps+1) --
+    def _legacy(self, run, kmax, nT, first_err=1):
+        """Run one trajectory; with self.verbose also fetch the per-iteration errors for the progress lines."""
+        eh = None
+        if self.verbose:
+            eh = torch.full((1, int(nT), int(kmax)), float("nan"), dtype=torch.float64, device=self.device)
+        U, it = run(eh)
+        self.last_iters = it[0].cpu().numpy()
+        Un = np.ascontiguousarray(U[0].cpu().numpy().T)
+        return Un, (eh[0].cpu().numpy() if eh is not None else None)
+
+    def _print_picard(self, At, errs):
+        """The lines of FEM/fem_burgers.py:659, 664 (= :722, 727): the error printed before iteration k is the one
+        iteration k-1 produced (1 before the first)."""
+        for n, k in enumerate(self.last_iters):
+            print(f"Time Step: {n}. Time: {n * At}")
+            for j in range(max(int(k), 0)):
+                print(f"Iteration: {j}, Error: {1 if j == 0 else errs[n, j - 1]}")
+
+    def _check_finite(self, what, singular=False):
+        """Non-finite trajectories are flagged, not raised, by the batched surface.  The single-sample drop-ins keep
+        the reference's behaviour: np.linalg.solve raises LinAlgError on a singular reduced system (:767, :1161);
+        the sparse FOM solve only warns (SuperLU) and goes on with nan."""
+        bad = np.flatnonzero(self.last_iters < 0)
+        if bad.size == 0:
+            return
+        if singular:
+            raise np.linalg.LinAlgError(f"Singular matrix ({what}: reduced system not finite at time step {int(bad[0])})")
+        import warnings
+        warnings.warn(f"{what}: state not finite from time step {int(bad[0])} on (matrix is exactly singular / "
+                      "iteration diverged)", RuntimeWarning, stacklevel=3)
+
     def fom_burgers(self, At, nTimeSteps, u0, mu1, E, mu2):
         """Drop-in for FEMBurgers.fom_burgers: returns ndarray (N, nTimeSteps+1)."""
-        U, it = self.fom_burgers_batch(At, nTimeSteps, np.asarray(u0, dtype=np.float64), [float(mu1)], E,
-                                       [float(mu2)])
-        self.last_iters = it[0].cpu().numpy()
-        return np.ascontiguousarray(U[0].cpu().numpy().T)
+        U, errs = self._legacy(lambda eh: self.fom_burgers_batch(At, nTimeSteps, np.asarray(u0, dtype=np.float64),
+                                                                 [float(mu1)], E, [float(mu2)], err_hist=eh),
+                               20, nTimeSteps)
+        if self.verbose:
+            self._print_picard(At, errs)
+        self._check_finite("fom_burgers")
+        return U
 
     def fom_burgers_newton(self, At, nTimeSteps, u0, mu1, E, mu2):
         """Drop-in for FEMBurgers.fom_burgers_newton (:584-643): returns ndarray (N, nTimeSteps+1)."""
         U, it = self.fom_burgers_newton_batch(At, nTimeSteps, np.asarray(u0, dtype=np.float64), [float(mu1)], E,
                                               [float(mu2)])
         self.last_iters = it[0].cpu().numpy()
+        self._check_finite("fom_burgers_newton")
         return np.ascontiguousarray(U[0].cpu().numpy().T)
 
     def pod_prom_burgers(self, At, nTimeSteps, u0, mu1, E, mu2, Phi, projection="Galerkin"):
         """Drop-in for FEMBurgers.pod_prom_burgers (:709-785): returns ndarray (N, nTimeSteps+1)."""
-        U, it = self.pod_prom_burgers_batch(At, nTimeSteps, np.asarray(u0, dtype=np.float64), [float(mu1)], E,
-                                            [float(mu2)], np.asarray(Phi, dtype=np.float64), projection)
-        self.last_iters = it[0].cpu().numpy()
-        return np.ascontiguousarray(U[0].cpu().numpy().T)
+        Phi = np.asarray(Phi, dtype=np.float64)
+        U, errs = self._legacy(lambda eh: self.pod_prom_burgers_batch(At, nTimeSteps, np.asarray(u0, dtype=np.float64),
+                                                                      [float(mu1)], E, [float(mu2)], Phi, projection,
+                                                                      err_hist=eh), 20, nTimeSteps)
+        if self.verbose:
+            self._print_picard(At, errs)
+        self._check_finite("pod_prom_burgers", singular=True)
+        return U
 
     def pod_quadratic_manifold(self, At, nTimeSteps, u0, uxa, E, mu2, Phi, H, projection="LSPG",
                                newton_tol=1e-6, newton_itmax=25):
         """Drop-in for FEMBurgers.pod_quadratic_manifold (:1081-1175): returns ndarray (N, nTimeSteps+1)."""
-        U, it = self.pod_quadratic_manifold_batch(At, nTimeSteps, np.asarray(u0, dtype=np.float64), [float(uxa)], E,
-                                                  [float(mu2)], np.asarray(Phi, dtype=np.float64),
-                                                  np.asarray(H, dtype=np.float64), projection,
-                                                  newton_tol=newton_tol, newton_itmax=newton_itmax)
-        self.last_iters = it[0].cpu().numpy()
-        return np.ascontiguousarray(U[0].cpu().numpy().T)
+        Phi = np.asarray(Phi, dtype=np.float64); H = np.asarray(H, dtype=np.float64)
+        U, errs = self._legacy(lambda eh: self.pod_quadratic_manifold_batch(
+            At, nTimeSteps, np.asarray(u0, dtype=np.float64), [float(uxa)], E, [float(mu2)], Phi, H, projection,
+            newton_tol=newton_tol, newton_itmax=newton_itmax, err_hist=eh), newton_itmax, nTimeSteps)
+        if self.verbose:   # the lines of :1127, :1166, :1171
+            for m, k in enumerate(self.last_iters):
+                print(f"\n=== time step {m+1}/{nTimeSteps}  (t = {(m+1)*At:.2f}) ===")
+                for it in range(max(int(k), 0)):
+                    print(f"  Newton {it:2d}:  |δq|/|q| = {errs[m, it]:.3e}")
+                if k == newton_itmax and not (errs[m, k - 1] < newton_tol):
+                    print("  Warning: Newton did not converge")
+        self._check_finite("pod_quadratic_manifold", singular=True)
+        return U
 
     # the north_star's name for the same method
     pod_prom_newton = pod_prom_burgers

@@ -65,11 +65,14 @@ class GramAccumulator:
         need = int(lib.bx_gram_workspace_bytes(self.N, cols))
         if need < 0:
             raise _lib.BurgersB200Error("bx_gram_workspace_bytes failed: " + lib.bx_last_error().decode())
-        if self._ws is None or self._ws.numel() < need:
-            self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
-        _lib.check(lib.bx_gram_accumulate(self.N, cols, U.data_ptr(), self.G.data_ptr(), 1,
-                                          self._ws.data_ptr(), torch.cuda.current_stream().cuda_stream),
-                   "bx_gram_accumulate")
+        if U.device != self.device:
+            raise ValueError(f"snapshots live on {U.device}, the accumulator on {self.device}")
+        with torch.cuda.device(self.device):   # the library launches on the current device
+            if self._ws is None or self._ws.numel() < need:
+                self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+            _lib.check(lib.bx_gram_accumulate(self.N, cols, U.data_ptr(), self.G.data_ptr(), 1,
+                                              self._ws.data_ptr(), torch.cuda.current_stream(self.device).cuda_stream),
+                       "bx_gram_accumulate")
         self.cols += cols
         return self
 
@@ -88,16 +91,60 @@ def allreduce_gram(G: torch.Tensor, group=None) -> torch.Tensor:
     return G
 
 
-def basis_from_gram(G: torch.Tensor, n_modes: int | None = None):
+GRAM_SAFETY = 64.0   # a mode is trusted while lam_k > GRAM_SAFETY * N * eps * lam_1
+
+
+def gram_resolved_modes(lam_desc: torch.Tensor) -> int:
+    """How many leading modes the Gram route determines: forming S S^T squares the condition number, so
+    eigenvalues below ~N eps lam_1 (sigma_k / sigma_1 below ~1e-7 at N = 512) are rounding noise."""
+    N = lam_desc.numel()
+    floor = GRAM_SAFETY * N * torch.finfo(torch.float64).eps * float(lam_desc[0])
+    return int((lam_desc > floor).sum().item())
+
+
+def basis_from_gram(G: torch.Tensor, n_modes: int | None = None, strict: bool = False):
     """eigh(G) -> (Phi, s): columns of Phi = left singular vectors of S in descending order,
-    s = singular values (POD/pod.py:84 returns the same pair from the SVD).  Runs where G lives."""
+    s = singular values (POD/pod.py:84 returns the same pair from the SVD).  Runs where G lives.
+    Limit of the Gram route: modes with sigma_k / sigma_1 below ~1e-7 are not resolved (enough for every
+    truncation the reference ships, eps^2 >= 1e-6 -> <= 227 modes, sigma_227 / sigma_1 = 1.9e-4; not for the full
+    498-column `U_modes_tol_0e+00`).  Asking for more modes than are resolved warns (raises with strict=True);
+    use `pod_basis_svd` for deep truncations."""
     lam, V = torch.linalg.eigh(G)
     lam = torch.flip(lam, dims=(0,))
     V = torch.flip(V, dims=(1,))
     s = torch.sqrt(torch.clamp(lam, min=0.0))
     if n_modes is not None:
+        ok = gram_resolved_modes(lam)
+        if n_modes > ok:
+            msg = (f"the Gram route resolves {ok} modes of this snapshot set (lam_k > {GRAM_SAFETY:g} N eps lam_1); "
+                   f"{n_modes} were requested — modes beyond {ok} are rounding noise, use pod_basis_svd")
+            if strict:
+                raise ValueError(msg)
+            import warnings
+            warnings.warn(msg, RuntimeWarning, stacklevel=2)
         V, s = V[:, :n_modes], s[:n_modes]
     return V.contiguous(), s
+
+
+def pod_basis_svd(snapshot_buffers, n_modes: int | None = None):
+    """Deep truncations (sigma_k / sigma_1 < 1e-7): tall-skinny QR of the snapshot rows + SVD of the small R factor
+    (cuSOLVER through torch.linalg — an offline library route, the same one burgers_b200.quadratic uses); no
+    squared condition number.  Single GPU: all buffers must live on one device."""
+    if isinstance(snapshot_buffers, torch.Tensor):
+        snapshot_buffers = [snapshot_buffers]
+    N = snapshot_buffers[0].shape[-1]
+    R = None
+    for U in snapshot_buffers:
+        rows = U.reshape(-1, N)
+        for lo in range(0, rows.shape[0], 1 << 17):
+            blk = rows[lo:lo + (1 << 17)]
+            stack = blk if R is None else torch.cat([R, blk], dim=0)
+            R = torch.linalg.qr(stack, mode="r").R
+    _, s, Vh = torch.linalg.svd(R, full_matrices=False)
+    V = Vh.transpose(0, 1).contiguous()
+    if n_modes is not None:
+        V, s = V[:, :n_modes].contiguous(), s[:n_modes]
+    return V, s
 
 
 def pod_basis(snapshot_buffers, n_modes: int | None = None, group=None):
@@ -124,11 +171,15 @@ def load_snapshot_directory(directory, device=None, prefix="fem_simulation_"):
     return torch.cat(blocks, dim=0).contiguous(), files
 
 
-def save_modes(U, s, tolerances_squared, snapshots_shape=None, directory="modes"):
-    """POD/pod.py:68-78: one `U_modes_tol_{eps2:.0e}.npy` + `Singular_values_modes_tol_*.npy` per tolerance."""
+def save_modes(U, s, tolerances_squared, snapshots=None, directory="modes"):
+    """POD/pod.py:68-78: one `U_modes_tol_{eps2:.0e}.npy` + `Singular_values_modes_tol_*.npy` per tolerance.
+    `snapshots`: the reference passes the snapshot MATRIX as the 4th positional argument
+    (`save_modes(U, s, eps2_tols, all_snapshots)`, POD/pod.py:90) and only reads its shape; an array, a tensor or
+    a plain (M, N) tuple are all accepted."""
     U = U.cpu().numpy() if isinstance(U, torch.Tensor) else np.asarray(U)
     s = s.cpu().numpy() if isinstance(s, torch.Tensor) else np.asarray(s)
-    M, N = snapshots_shape if snapshots_shape is not None else (U.shape[0], s.size)
+    shape = getattr(snapshots, "shape", snapshots)
+    M, N = tuple(shape)[:2] if shape is not None else (U.shape[0], s.size)
     taken = get_list_of_number_of_singular_values_for_list_of_tolerances(tolerances_squared, s, M, N)
     os.makedirs(directory, exist_ok=True)
     out = []

@@ -99,6 +99,15 @@ def sweep_to_npy(fem, directory, At, nTimeSteps, u0, mu1, mu2, E=0.0, chunk=256,
     compute = torch.cuda.current_stream()
     iters = np.empty((B, nT), dtype=np.int32)
     paths = [os.path.join(directory, name(float(a), float(b))) for a, b in zip(mu1, mu2)]
+    if len(set(paths)) != B:   # two samples that round to the same .3f / .4f name would race in the writer pool
+        seen, dup = set(), None
+        for q in paths:
+            if q in seen:
+                dup = q
+                break
+            seen.add(q)
+        raise ValueError(f"two samples map to the same file name {os.path.basename(dup)!r}; pass a `name` function "
+                         "with more digits")
     copied = [None, None]
     pending = [None, None]
     futures = [[], []]

@@ -23,6 +23,11 @@
  *     per-sample layout (N, nsteps+1) (FEM/fem_burgers.py:650) is its transpose.
  *   - iteration counts: iters[b][step], int32, the number of nonlinear iterations the
  *     reference's while-loop would have executed for that step.
+ *   - non-finite states never abort a batch: from the first step of sample b whose state is not
+ *     finite (overflowing Picard iteration, singular reduced system — where the reference prints nan
+ *     or raises numpy.linalg.LinAlgError, FEM/fem_burgers.py:767), iters[b][step] = -1 and the
+ *     snapshots are NaN; the other samples are unaffected.
+ *   - a workspace must not be shared by launches that may run concurrently (one per stream).
  */
 #ifndef BURGERS_B200_H
 #define BURGERS_B200_H
@@ -45,6 +50,29 @@ int         bx_version(void);
 const char *bx_last_error(void);
 /* number of SMs / device name of the current device (diagnostics for bench.py) */
 int         bx_device_sm_count(void);
+
+/* ---- explicit tuning knobs -------------------------------------------------------------------
+ * Launch-shape choices are automatic; these knobs force one for A/B measurements and for tests that
+ * must reach every instance.  Process-wide, value < 0 (the default) = automatic.  They replace the
+ * environment switches of round 1: nothing on the launch path reads the environment.               */
+#define BX_TUNE_FOM_WARPS_PER_TRAJECTORY 0  /* 1, 2 or 4 warps integrate one FOM trajectory (N <= 512)   */
+#define BX_TUNE_PROM_CTA_WARPS           1  /* 8 or 16 warps per trajectory, POD PROM with n >= 32        */
+#define BX_TUNE_PROM_CTA_CHUNK           2  /* 8, 12, 16, 24 or 32 nodes per staged Phi chunk, n >= 32   */
+#define BX_TUNE_QM_SCHEDULE              3  /* tangent rows of the quadratic-manifold PROM:
+                                               0 global scratch, 1 shared-memory tile, 2 chunked global   */
+#define BX_TUNE_PROM_WARPS_PER_TRAJECTORY 4 /* 1 or 2 warps integrate one POD-PROM trajectory (n <= 31)   */
+#define BX_TUNE_COUNT                    8
+int bx_set_tuning(int knob, int value);
+int bx_get_tuning(int knob);
+
+/* ---- FP64 peak probe (roofline denominators; MEASURED_PEAKS.json has no FP64 entry) --------------
+ * Launches a saturating stream of independent DFMA (kind BX_PROBE_DFMA) or mma.sync.m8n8k4.f64
+ * (BX_PROBE_DMMA) instructions on `stream` (16 warps per SM, `iters` rounds) and returns the number of
+ * floating-point operations the launch executes (negative BX_ERR_* on error).  The caller times it
+ * with events on the same stream: peak = flops / seconds.  sink: one device double (never written). */
+#define BX_PROBE_DFMA 0
+#define BX_PROBE_DMMA 1
+long long bx_probe_fp64_peak(int kind, int iters, double *sink, void *stream);
 
 /* ---- L1 operators -------------------------------------------------------------------- */
 /* FEMBurgers.compute_mass_matrix, FEM/fem_burgers.py:324-353 */
@@ -83,11 +111,16 @@ long long bx_workspace_bytes(void);
 /* FEMBurgers.fom_burgers, FEM/fem_burgers.py:646-707, for B samples at once.
  * u0: (N,) shared by all samples when u0_batched == 0, else (B, N).
  * tol, kmax: the literals 1e-6 / 20 of :663.  U: (B, nsteps+1, N).  iters: (B, nsteps) or NULL.
+ * err_hist: NULL, or (B, nsteps, kmax): entry [b][step][k] receives |delta_U| / |U1| after iteration k
+ * (the value the reference prints as "Iteration: k+1, Error: ..." at :664); entries of iterations that
+ * did not run are left untouched.
+ * N <= 1024.  One, two or four warps integrate one trajectory (chosen from B and the SM count;
+ * BX_TUNE_FOM_WARPS_PER_TRAJECTORY forces it).
  * workspace: bx_workspace_bytes() bytes (contents ignored, overwritten).                  */
 int bx_fom_picard_trajectories(int B, int N, int nsteps, const double *X, const double *u0,
                                int u0_batched, const double *mu1, const double *mu2,
                                double At, double E, double tol, int kmax,
-                               double *U, int *iters, void *workspace, void *stream);
+                               double *U, int *iters, double *err_hist, void *workspace, void *stream);
 
 /* FEMBurgers.fom_burgers, FEM/fem_burgers.py:646-707, on a mesh too large for one warp (N > 1024;
  * BASELINE config 5: 2^20 nodes): one persistent cooperative kernel per call, the N x N tridiagonal solve
@@ -105,7 +138,8 @@ int bx_fom_picard_finemesh(int B, int N, int nsteps, const double *X, const doub
  * projection: BX_GALERKIN (Ar = Phi^T A Phi, br = Phi^T R, :756-757) or BX_LSPG (J = A Phi,
  * Ar = J^T J, br = J^T R, :760-762); anything else returns BX_ERR_PROJECTION (ValueError, :764).
  * The reduced solve is LU with partial pivoting (np.linalg.solve -> LAPACK gesv, :767).
- * tol, kmax: the literals 1e-6 / 20 of :725.  1 <= n <= 240 (the reference's stored truncations have
+ * tol, kmax: the literals 1e-6 / 20 of :725.  err_hist: NULL or (B, nsteps, kmax), |dq| / |q| after every
+ * iteration (the value printed at :727).  1 <= n <= 240 (the reference's stored truncations have
  * 9 ... 227 modes, POD/modes/): n <= 31 runs one warp per trajectory with Phi in shared memory, n >= 32
  * one CTA per trajectory with Phi streamed from L2 and a blocked LU of the reduced system.
  * workspace: bx_prom_workspace_bytes(B, N, n) bytes (work queue, per-sample forcing data and, for
@@ -114,7 +148,7 @@ long long bx_prom_workspace_bytes(int B, int N, int n);
 int bx_prom_trajectories(int B, int N, int n, int nsteps, const double *X, const double *u0,
                          int u0_batched, const double *mu1, const double *mu2, double At, double E,
                          const double *Phi, int projection, double tol, int kmax,
-                         double *U, int *iters, void *workspace, void *stream);
+                         double *U, int *iters, double *err_hist, void *workspace, void *stream);
 
 /* FEMBurgers.pod_quadratic_manifold, FEM/fem_burgers.py:1081-1175, for B samples at once.
  * Decoder u = Phi q + H sym(q x q), tangent Phi + H dQ/dq (get_single_Q / get_dQ_dq, :275-312; monomial
@@ -123,13 +157,16 @@ int bx_prom_trajectories(int B, int N, int n, int nsteps, const double *X, const
  * No SUPG term (:1141); q accumulates over the Gauss-Newton iterations and is re-projected from the full
  * state at every time step (:1129); stops when |dq| / max(1e-14, |q|) < tol (strict, :1165-1169) or after
  * itmax iterations; iters[b][step] = iterations executed.  projection: BX_GALERKIN / BX_LSPG, anything
- * else BX_ERR_PROJECTION (ValueError, :1158).  1 <= n <= 31 in this build.
+ * else BX_ERR_PROJECTION (ValueError, :1158).  err_hist: NULL or (B, nsteps, itmax), the value printed at :1166.
+ * 1 <= n <= 31 in this build.
  * workspace: bx_qm_workspace_bytes(B, N, n) bytes, 16-byte aligned, contents ignored.               */
 long long bx_qm_workspace_bytes(int B, int N, int n);
 int bx_qm_prom_trajectories(int B, int N, int n, int nsteps, const double *X, const double *u0,
                             int u0_batched, const double *uxa, const double *mu2, double At, double E,
                             const double *Phi, const double *H, int projection, double tol, int itmax,
-                            double *U, int *iters, void *workspace, void *stream);
+                            double *U, int *iters, double *err_hist, void *workspace, void *stream);
+/* 1 if tangent-row schedule `schedule` (BX_TUNE_QM_SCHEDULE) can run at (N, n) on the current device */
+int bx_qm_schedule_available(int N, int n, int schedule);
 
 /* FEMBurgers.fom_burgers_newton AS CODED, FEM/fem_burgers.py:584-643, for B samples at once.
  * At :616 `At * dC_dU @ U0` is a matrix-vector product whose result numpy broadcasts onto every row:

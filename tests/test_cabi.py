@@ -42,12 +42,29 @@ def test_version_and_workspace(lib):
 def test_argument_validation_without_gpu(lib):
     # invalid sizes are rejected before any CUDA call is made
     assert lib.bx_fom_picard_trajectories(4, 1, 10, None, None, 0, None, None, 0.05, 0.0, 1e-6, 20,
-                                          None, None, None, None) == -1
+                                          None, None, None, None, None) == -1
     assert b"2 nodes" in lib.bx_last_error()
     assert lib.bx_fom_picard_trajectories(4, 512, 10, None, None, 0, None, None, 0.05, 0.0, 1e-6, 0,
-                                          None, None, None, None) == -1
+                                          None, None, None, None, None) == -1
     assert lib.bx_tridiag_solve_update(1, 4096, None, None, None, None, None, None, None, None) == -1
     assert lib.bx_mass_bands(1, None, None, None, None, None) == -1
+
+
+def test_tuning_knobs_are_an_explicit_api(lib):
+    """Launch-shape switches are set through bx_set_tuning, not the environment."""
+    import burgers_b200
+    for knob in burgers_b200._lib.TUNING_KNOBS:
+        assert burgers_b200.get_tuning(knob) == -1
+        burgers_b200.set_tuning(knob, 2)
+        assert burgers_b200.get_tuning(knob) == 2
+        burgers_b200.set_tuning(knob, -5)
+        assert burgers_b200.get_tuning(knob) == -1
+    assert lib.bx_set_tuning(99, 1) == -1
+    with pytest.raises(KeyError):
+        burgers_b200.set_tuning("no_such_knob", 1)
+    src = "".join(open(os.path.join(ROOT, "1d-burgers-equation-roms_b200", "csrc", f)).read()
+                  for f in os.listdir(os.path.join(ROOT, "1d-burgers-equation-roms_b200", "csrc")))
+    assert "getenv" not in src
 
 
 def test_mesh_validation():

@@ -35,11 +35,18 @@ def test_prom_sweeps_are_bitwise_reproducible(n, proj, oracle):
     assert int(it.min()) >= 1
 
 
-@pytest.mark.parametrize("mode", ["default", "0", "1", "2"])
-def test_qm_sweeps_are_bitwise_reproducible(mode, oracle, monkeypatch):
+@pytest.fixture
+def qm_schedule():
+    """Force a tangent-row schedule of csrc/bx_qm.cu (v2 / shared tile / chunked global) for one test."""
     import burgers_b200
-    if mode != "default":
-        monkeypatch.setenv("BX_QM_TS", mode)     # A/B switch of csrc/bx_qm.cu: v2 / shared tile / chunked global
+    yield lambda mode: burgers_b200.set_tuning("qm_schedule", mode)
+    burgers_b200.set_tuning("qm_schedule", -1)
+
+
+@pytest.mark.parametrize("mode", [-1, 0, 1, 2])
+def test_qm_sweeps_are_bitwise_reproducible(mode, oracle, qm_schedule):
+    import burgers_b200
+    qm_schedule(mode)
     X, _ = oracle.mesh(512)
     fem = burgers_b200.FEMBurgers(X)
     Phi = np.load(f"{GOLDEN}/qm_Phi.npy"); H = np.load(f"{GOLDEN}/qm_H.npy")
@@ -47,7 +54,21 @@ def test_qm_sweeps_are_bitwise_reproducible(mode, oracle, monkeypatch):
     _twice(lambda: fem.pod_quadratic_manifold_batch(0.05, 8, np.ones(512), mu1, 0.0, mu2, Phi, H, "LSPG"))
 
 
-def test_qm_modes_agree_with_each_other(oracle, monkeypatch):
+@pytest.mark.parametrize("W", [2, 4])
+def test_multiwarp_fom_sweeps_are_bitwise_reproducible(W, oracle):
+    """The 2- and 4-warps-per-trajectory FOM instances synchronise through named barriers and shared memory."""
+    import burgers_b200
+    X, _ = oracle.mesh(512)
+    fem = burgers_b200.FEMBurgers(X)
+    mu1, mu2 = oracle.parameter_grid(37, 41)     # 1517 samples: several per resident group
+    burgers_b200.set_tuning("fom_warps_per_trajectory", W)
+    try:
+        _twice(lambda: fem.fom_burgers_batch(0.05, 12, np.ones(512), mu1, 0.0, mu2))
+    finally:
+        burgers_b200.set_tuning("fom_warps_per_trajectory", -1)
+
+
+def test_qm_modes_agree_with_each_other(oracle, qm_schedule):
     """The three tangent-row paths of the QM kernel are different schedules of the same arithmetic up to the
     summation order of u; they must agree to rounding and give the same iteration counts."""
     import torch
@@ -57,11 +78,11 @@ def test_qm_modes_agree_with_each_other(oracle, monkeypatch):
     Phi = np.load(f"{GOLDEN}/qm_Phi.npy"); H = np.load(f"{GOLDEN}/qm_H.npy")
     mu1, mu2 = oracle.parameter_grid(5, 5)
     res = {}
-    for mode in ("0", "1", "2"):
-        monkeypatch.setenv("BX_QM_TS", mode)
+    for mode in (0, 1, 2):
+        qm_schedule(mode)
         U, it = fem.pod_quadratic_manifold_batch(0.05, 10, np.ones(512), mu1, 0.0, mu2, Phi, H, "Galerkin")
         res[mode] = (U.clone(), it.clone())
-    for mode in ("1", "2"):
-        assert torch.equal(res[mode][1], res["0"][1])
-        rel = ((res[mode][0] - res["0"][0]).norm(dim=2) / res["0"][0].norm(dim=2)).max()
+    for mode in (1, 2):
+        assert torch.equal(res[mode][1], res[0][1])
+        rel = ((res[mode][0] - res[0][0]).norm(dim=2) / res[0][0].norm(dim=2)).max()
         assert float(rel) <= 1e-10

@@ -107,3 +107,58 @@ def test_config2_slice_properties(oracle, fem512):
     Uo, ito = oracle.fom_burgers_batch(X, 0.05, 4, np.ones(512), mu1[sel], 0.0, mu2[sel])
     assert np.array_equal(itc[sel], ito)
     assert np.max(np.linalg.norm(Uc[sel] - Uo, axis=2) / np.linalg.norm(Uo, axis=2)) <= TOL
+
+
+@pytest.fixture
+def warps_per_trajectory():
+    import burgers_b200
+    yield lambda W: burgers_b200.set_tuning("fom_warps_per_trajectory", W)
+    burgers_b200.set_tuning("fom_warps_per_trajectory", -1)
+
+
+@pytest.mark.parametrize("W", [1, 2, 4])
+def test_multiwarp_all_14_stored_fixtures_full_500_steps(W, golden, fem512, warps_per_trajectory):
+    """Every warps-per-trajectory instance forced explicitly (the automatic choice takes 4 / 2 warps for sweeps with
+    few trajectories per GPU, 1 for full sweeps) against the reference's stored fixtures over all 500 steps: same
+    tolerance, identical iteration counts."""
+    g = golden("fom_fixtures.npz")
+    pts = g["points"]
+    warps_per_trajectory(W)
+    U, it = fem512.fom_burgers_batch(0.05, 500, np.ones(512), pts[:, 0], 0.0, pts[:, 1])
+    U = U.cpu().numpy(); it = it.cpu().numpy()
+    for i in range(14):
+        assert rel_l2_per_step(U[i].T[:, g["steps"]], g[f"U_{i}"]) <= TOL, i
+        assert np.array_equal(it[i], g[f"it_{i}"].astype(np.int32)), i
+
+
+@pytest.mark.parametrize("W", [1, 2, 4])
+@pytest.mark.parametrize("N", [129, 200, 256, 257, 300, 511, 512, 513, 700, 1023, 1024])
+def test_multiwarp_sizes_vs_oracle(W, N, oracle, warps_per_trajectory):
+    import burgers_b200
+    X = np.linspace(0.0, 100.0 * (N - 1) / 511.0, N)
+    fem = burgers_b200.FEMBurgers(X)
+    mu1 = np.array([4.3, 5.1, 4.75, 5.4, 4.6]); mu2 = np.array([0.016, 0.029, 0.02, 0.017, 0.026])
+    warps_per_trajectory(W)
+    U, it = fem.fom_burgers_batch(0.05, 5, np.ones(N), mu1, 0.0, mu2)
+    Uo, ito = oracle.fom_burgers_batch(X, 0.05, 5, np.ones(N), mu1, 0.0, mu2)
+    assert np.array_equal(it.cpu().numpy(), ito)
+    err = np.max(np.linalg.norm(U.cpu().numpy() - Uo, axis=2) / np.linalg.norm(Uo, axis=2))
+    assert err <= TOL
+
+
+def test_multiwarp_nonuniform_mesh_and_automatic_dispatch(golden, oracle, warps_per_trajectory):
+    """Non-uniform mesh with E != 0 through the multi-warp instances, and the automatic choice (few samples ->
+    several warps per trajectory) against the oracle."""
+    import burgers_b200
+    rng = np.random.default_rng(11)
+    X = np.sort(np.concatenate([[0.0, 100.0], 100.0 * rng.random(398)]))
+    N = X.size
+    fem = burgers_b200.FEMBurgers(X)
+    mu1 = np.array([4.4, 5.2, 4.8]); mu2 = np.array([0.017, 0.027, 0.021])
+    u0 = 1.0 + 0.05 * rng.random((3, N))
+    Uo, ito = oracle.fom_burgers_batch(X, 0.02, 6, u0, mu1, 0.01, mu2)
+    for W in (2, 4, -1):
+        warps_per_trajectory(W)
+        U, it = fem.fom_burgers_batch(0.02, 6, u0, mu1, 0.01, mu2)
+        assert np.array_equal(it.cpu().numpy(), ito), W
+        assert np.max(np.linalg.norm(U.cpu().numpy() - Uo, axis=2) / np.linalg.norm(Uo, axis=2)) <= TOL, W
