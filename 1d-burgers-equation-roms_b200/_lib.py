@@ -14,7 +14,8 @@ BX_GALERKIN, BX_LSPG = 0, 1
 BX_PROBE_DFMA, BX_PROBE_DMMA = 0, 1
 # bx_set_tuning knobs (include/burgers_b200.h)
 TUNING_KNOBS = {"fom_warps_per_trajectory": 0, "prom_cta_warps": 1, "prom_cta_chunk": 2, "qm_schedule": 3,
-                "prom_warps_per_trajectory": 4}
+                "prom_warps_per_trajectory": 4, "fom_kernel": 5,
+                "fom_segment_steps": 6}
 
 P = c_void_p  # device pointer / stream
 
@@ -31,6 +32,7 @@ SIGNATURES = {
     "bx_assemble_picard": (c_int, [c_int, c_int, P, P, P, P, P, c_double, c_double, c_int, P, P, P, P, P, P]),
     "bx_tridiag_solve_update": (c_int, [c_int, c_int, P, P, P, P, P, P, P, P]),
     "bx_workspace_bytes": (c_longlong, []),
+    "bx_fom_workspace_bytes": (c_longlong, [c_int]),
     "bx_fom_picard_trajectories": (c_int, [c_int, c_int, c_int, P, P, c_int, P, P, c_double, c_double,
                                            c_double, c_int, P, P, P, P, P]),
     "bx_fine_workspace_bytes": (c_longlong, [c_int]),

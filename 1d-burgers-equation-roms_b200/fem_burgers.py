@@ -273,7 +273,8 @@ class FEMBurgers:
             return U, iters
         _lib.check(lib.bx_fom_picard_trajectories(B, N, nT, _ptr(self.Xd), _ptr(u0), batched, _ptr(mu1),
                                                   _ptr(mu2), float(At), float(E), float(tol), int(kmax),
-                                                  _ptr(U), _ptr(iters), _ptr(eh), _ptr(self._workspace()),
+                                                  _ptr(U), _ptr(iters), _ptr(eh),
+                                                  _ptr(self._scratch(int(lib.bx_fom_workspace_bytes(B)))),
                                                   self._stream()),
                    "bx_fom_picard_trajectories")
         return U, iters

@@ -61,6 +61,8 @@ int         bx_device_sm_count(void);
 #define BX_TUNE_QM_SCHEDULE              3  /* tangent rows of the quadratic-manifold PROM:
                                                0 global scratch, 1 shared-memory tile, 2 chunked global   */
 #define BX_TUNE_PROM_WARPS_PER_TRAJECTORY 4 /* 1 or 2 warps integrate one POD-PROM trajectory (n <= 31)   */
+#define BX_TUNE_FOM_KERNEL               5  /* 0 throughput kernel, 1 latency kernel (speculative front half) */
+#define BX_TUNE_FOM_SEGMENT_STEPS        6  /* time steps per work unit of the throughput kernel (0: whole trajectories) */
 #define BX_TUNE_COUNT                    8
 int bx_set_tuning(int knob, int value);
 int bx_get_tuning(int knob);
@@ -114,9 +116,12 @@ long long bx_workspace_bytes(void);
  * err_hist: NULL, or (B, nsteps, kmax): entry [b][step][k] receives |delta_U| / |U1| after iteration k
  * (the value the reference prints as "Iteration: k+1, Error: ..." at :664); entries of iterations that
  * did not run are left untouched.
- * N <= 1024.  One, two or four warps integrate one trajectory (chosen from B and the SM count;
- * BX_TUNE_FOM_WARPS_PER_TRAJECTORY forces it).
- * workspace: bx_workspace_bytes() bytes (contents ignored, overwritten).                  */
+ * N <= 1024.  Sweeps that fill the device run one warp per trajectory in round-robin segments of
+ * BX_TUNE_FOM_SEGMENT_STEPS time steps (csrc/bx_fom.cu); sweeps with at most 8 trajectories per SM run the
+ * latency kernel (csrc/bx_fom_strong.cu) with one, two or four warps per trajectory
+ * (BX_TUNE_FOM_KERNEL / BX_TUNE_FOM_WARPS_PER_TRAJECTORY force the choice).
+ * workspace: bx_fom_workspace_bytes(B) bytes (contents ignored, overwritten).             */
+long long bx_fom_workspace_bytes(int B);
 int bx_fom_picard_trajectories(int B, int N, int nsteps, const double *X, const double *u0,
                                int u0_batched, const double *mu1, const double *mu2,
                                double At, double E, double tol, int kmax,

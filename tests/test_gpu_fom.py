@@ -112,18 +112,25 @@ def test_config2_slice_properties(oracle, fem512):
 @pytest.fixture
 def warps_per_trajectory():
     import burgers_b200
-    yield lambda W: burgers_b200.set_tuning("fom_warps_per_trajectory", W)
+
+    def force(W, kernel=-1):
+        """W warps per trajectory; kernel 0 = throughput kernel (bx_fom.cu), 1 = latency kernel (bx_fom_strong.cu),
+        -1 = the library's own choice by batch size"""
+        burgers_b200.set_tuning("fom_warps_per_trajectory", W)
+        burgers_b200.set_tuning("fom_kernel", kernel)
+    yield force
     burgers_b200.set_tuning("fom_warps_per_trajectory", -1)
+    burgers_b200.set_tuning("fom_kernel", -1)
 
 
-@pytest.mark.parametrize("W", [1, 2, 4])
-def test_multiwarp_all_14_stored_fixtures_full_500_steps(W, golden, fem512, warps_per_trajectory):
-    """Every warps-per-trajectory instance forced explicitly (the automatic choice takes 4 / 2 warps for sweeps with
-    few trajectories per GPU, 1 for full sweeps) against the reference's stored fixtures over all 500 steps: same
-    tolerance, identical iteration counts."""
+@pytest.mark.parametrize("W,kernel", [(1, 0), (1, 1), (2, 1), (4, 1)])
+def test_multiwarp_all_14_stored_fixtures_full_500_steps(W, kernel, golden, fem512, warps_per_trajectory):
+    """The throughput kernel (kernel 0, one warp per trajectory) and every warps-per-trajectory instance of the
+    latency kernel (kernel 1; the automatic choice takes it for sweeps with few trajectories per SM) forced
+    explicitly, against the reference's stored fixtures over all 500 steps: same tolerance, identical counts."""
     g = golden("fom_fixtures.npz")
     pts = g["points"]
-    warps_per_trajectory(W)
+    warps_per_trajectory(W, kernel)
     U, it = fem512.fom_burgers_batch(0.05, 500, np.ones(512), pts[:, 0], 0.0, pts[:, 1])
     U = U.cpu().numpy(); it = it.cpu().numpy()
     for i in range(14):
@@ -131,14 +138,14 @@ def test_multiwarp_all_14_stored_fixtures_full_500_steps(W, golden, fem512, warp
         assert np.array_equal(it[i], g[f"it_{i}"].astype(np.int32)), i
 
 
-@pytest.mark.parametrize("W", [1, 2, 4])
+@pytest.mark.parametrize("W,kernel", [(1, 0), (1, 1), (2, 1), (4, 1)])
 @pytest.mark.parametrize("N", [129, 200, 256, 257, 300, 511, 512, 513, 700, 1023, 1024])
-def test_multiwarp_sizes_vs_oracle(W, N, oracle, warps_per_trajectory):
+def test_multiwarp_sizes_vs_oracle(W, N, kernel, oracle, warps_per_trajectory):
     import burgers_b200
     X = np.linspace(0.0, 100.0 * (N - 1) / 511.0, N)
     fem = burgers_b200.FEMBurgers(X)
     mu1 = np.array([4.3, 5.1, 4.75, 5.4, 4.6]); mu2 = np.array([0.016, 0.029, 0.02, 0.017, 0.026])
-    warps_per_trajectory(W)
+    warps_per_trajectory(W, kernel)
     U, it = fem.fom_burgers_batch(0.05, 5, np.ones(N), mu1, 0.0, mu2)
     Uo, ito = oracle.fom_burgers_batch(X, 0.05, 5, np.ones(N), mu1, 0.0, mu2)
     assert np.array_equal(it.cpu().numpy(), ito)
@@ -157,8 +164,8 @@ def test_multiwarp_nonuniform_mesh_and_automatic_dispatch(golden, oracle, warps_
     mu1 = np.array([4.4, 5.2, 4.8]); mu2 = np.array([0.017, 0.027, 0.021])
     u0 = 1.0 + 0.05 * rng.random((3, N))
     Uo, ito = oracle.fom_burgers_batch(X, 0.02, 6, u0, mu1, 0.01, mu2)
-    for W in (2, 4, -1):
-        warps_per_trajectory(W)
+    for W, kernel in ((1, 1), (2, 1), (4, 1), (1, 0), (-1, -1)):
+        warps_per_trajectory(W, kernel)
         U, it = fem.fom_burgers_batch(0.02, 6, u0, mu1, 0.01, mu2)
-        assert np.array_equal(it.cpu().numpy(), ito), W
-        assert np.max(np.linalg.norm(U.cpu().numpy() - Uo, axis=2) / np.linalg.norm(Uo, axis=2)) <= TOL, W
+        assert np.array_equal(it.cpu().numpy(), ito), (W, kernel)
+        assert np.max(np.linalg.norm(U.cpu().numpy() - Uo, axis=2) / np.linalg.norm(Uo, axis=2)) <= TOL, (W, kernel)

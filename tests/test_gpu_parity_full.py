@@ -57,19 +57,24 @@ def test_qm_config4_path_vs_oracle(n, proj, oracle, fem512, training_snapshots):
     X, _ = oracle.mesh(512)
     Phi, H = _manifold(oracle, training_snapshots, n)
     nT = 12
-    ref = [oracle.pod_quadratic_manifold(X, 0.05, nT, np.ones(512), QM_MU1[b], 0.0, QM_MU2[b], Phi, H, proj)
-           for b in range(QM_MU1.size)]
-    assert max(int(r[1].max()) for r in ref) == 25, "the case must reach newton_itmax on some step"
-    for sched in burgers_b200.qm_schedules(512, n):
-        burgers_b200.set_tuning("qm_schedule", sched)
-        try:
-            U, it = fem512.pod_quadratic_manifold_batch(0.05, nT, np.ones(512), QM_MU1, 0.0, QM_MU2, Phi, H, proj)
-            U = U.cpu().numpy(); it = it.cpu().numpy()
-        finally:
-            burgers_b200.set_tuning("qm_schedule", -1)
-        for b, (Uo, ito) in enumerate(ref):
-            assert np.array_equal(it[b], ito), (sched, b, it[b], ito)
-            assert rel_l2_per_step(U[b].T, Uo) <= TOL, (sched, b)
+    # two passes: the reference's default cap (25, never reached here: the first step needs 18 at most) and a cap of 6,
+    # which the first steps of every sample reach (the ':1171' non-convergence branch of the reference)
+    for itmax in (25, 6):
+        ref = [oracle.pod_quadratic_manifold(X, 0.05, nT, np.ones(512), QM_MU1[b], 0.0, QM_MU2[b], Phi, H, proj,
+                                             1e-6, itmax) for b in range(QM_MU1.size)]
+        if itmax == 6:
+            assert max(int(r[1].max()) for r in ref) == 6, "the case must reach newton_itmax on some step"
+        for sched in burgers_b200.qm_schedules(512, n):
+            burgers_b200.set_tuning("qm_schedule", sched)
+            try:
+                U, it = fem512.pod_quadratic_manifold_batch(0.05, nT, np.ones(512), QM_MU1, 0.0, QM_MU2, Phi, H, proj,
+                                                            newton_itmax=itmax)
+                U = U.cpu().numpy(); it = it.cpu().numpy()
+            finally:
+                burgers_b200.set_tuning("qm_schedule", -1)
+            for b, (Uo, ito) in enumerate(ref):
+                assert np.array_equal(it[b], ito), (itmax, sched, b, it[b], ito)
+                assert rel_l2_per_step(U[b].T, Uo) <= TOL, (itmax, sched, b)
 
 
 @pytest.mark.parametrize("proj", ["Galerkin", "LSPG"])

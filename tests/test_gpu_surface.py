@@ -71,8 +71,9 @@ def test_verbose_off_prints_nothing(fem512):
 
 @pytest.mark.parametrize("W", [-1, 2, 4])
 def test_nonfinite_sample_is_flagged_and_the_batch_goes_on(W, oracle, fem512):
-    """One sample overflows (left boundary value 1e200: u^2 is inf); its steps carry -1 and NaN snapshots from the
-    first non-finite step on, the other samples of the batch equal the oracle."""
+    """One sample overflows (left boundary value 1e200: |U|^2 is inf, so the reference's error ratio is nan from the
+    first iteration on); its steps carry -1 from the first step whose norm is not finite and NaN snapshots after it,
+    the other samples of the batch equal the oracle."""
     import burgers_b200
     X, _ = oracle.mesh(512)
     mu1 = np.array([4.3, 1e200, 5.1, 4.75, 4.9]); mu2 = np.array([0.016, 0.02, 0.029, 0.02, 0.024])
@@ -84,7 +85,8 @@ def test_nonfinite_sample_is_flagged_and_the_batch_goes_on(W, oracle, fem512):
     U = U.cpu().numpy(); it = it.cpu().numpy()
     first = int(np.argmax(it[1] < 0))
     assert it[1, first] == -1 and (it[1, first:] == -1).all() and (it[1, :first] >= 1).all()
-    assert np.isnan(U[1, first + 2:]).all() and not np.isfinite(U[1, first + 1]).all()
+    with np.errstate(over="ignore"):
+        assert np.isnan(U[1, first + 2:]).all() and not np.isfinite(np.sum(U[1, first + 1] ** 2))
     for b in (0, 2, 3, 4):
         Uo, ito = oracle.fom_burgers(X, 0.05, 6, np.ones(512), mu1[b], 0.0, mu2[b])
         assert np.array_equal(it[b], ito) and rel_l2_per_step(U[b].T, Uo) <= TOL

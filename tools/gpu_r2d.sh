@@ -1,0 +1,22 @@
+#!/bin/bash
+TAG=${1:-r2d}
+OUT=gpurun_out/$TAG
+mkdir -p $OUT
+timeout 900 python -m pytest tests/test_gpu_fom.py tests/test_gpu_segments.py tests/test_gpu_surface.py tests/test_gpu_determinism.py -m gpu -q -x > $OUT/pytest_fom.log 2>&1; echo "pytest rc=$?" >> $OUT/pytest_fom.log
+tail -15 $OUT/pytest_fom.log
+for seg in 0 10 25 50 100; do
+python - <<PY >> $OUT/segments.txt 2>&1
+import sys; sys.path.insert(0, '.')
+import burgers_b200
+burgers_b200.set_tuning("fom_segment_steps", $seg)
+sys.argv = ["fom_one", "4096", "500", "0", "1", "5"]
+print("segment steps $seg:", end=" ")
+exec(open("tools/fom_one.py").read())
+sys.argv = ["fom_one", "2048", "500", "0", "1", "5"]
+print("segment steps $seg:", end=" ")
+exec(open("tools/fom_one.py").read())
+PY
+done
+cat $OUT/segments.txt
+timeout 600 python tools/fom_warps.py 500 148 296 512 1024 1184 1776 2048 4096 8192 > $OUT/fom_warps.txt 2>&1
+cat $OUT/fom_warps.txt
