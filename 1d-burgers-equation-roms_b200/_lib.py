@@ -33,6 +33,7 @@ SIGNATURES = {
     "bx_tridiag_solve_update": (c_int, [c_int, c_int, P, P, P, P, P, P, P, P]),
     "bx_workspace_bytes": (c_longlong, []),
     "bx_fom_workspace_bytes": (c_longlong, [c_int]),
+    "bx_fom_plan": (c_int, [c_int, c_int]),
     "bx_fom_picard_trajectories": (c_int, [c_int, c_int, c_int, P, P, c_int, P, P, c_double, c_double,
                                            c_double, c_int, P, P, P, P, P]),
     "bx_fine_workspace_bytes": (c_longlong, [c_int]),

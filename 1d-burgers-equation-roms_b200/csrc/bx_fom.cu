@@ -138,20 +138,23 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) fom_picard_kernel(const FomP
                 for (int j = 0; j < M; ++j) if (node0 + j < N) Us[j] = u[j];
             }
         } else {        // resume from the snapshot the previous segment's warp left in U
-            int done = 0;
-            if (lane == 0) {
-                const int *flag = p.progress + s;
-                for (;;) {
-                    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(done) : "l"(flag) : "memory");
-                    if (done >= g || done < 0) break;
-                    __nanosleep(200);
-                }
+            // every lane polls the same word (one broadcast transaction per probe; see the note at the publish
+            // store below for why this is not left to lane 0), then lane 0's value decides for the warp
+            int done;
+            {
+                const volatile int *flag = p.progress + s;
+                while ((done = *flag) < g && done >= 0) __nanosleep(200);
             }
             done = __shfl_sync(FULL, done, 0);
-            finite = done >= 0;     // a negative word: the trajectory stopped being finite in an earlier segment
+            __threadfence();        // acquire side: the snapshot loads below stay behind the flag read
+            // A negative word: the trajectory stopped being finite in an earlier segment.  Its state is poisoned
+            // here as DATA (a select, not a branch: a warp-level branch on the polled word costs the compiler its
+            // convergence proof for every shuffle of the hot loop), so the first step of this segment comes out
+            // non-finite, takes the flag -1 and the segment is filled with NaN like the ones before it.
+            const double poison = done < 0 ? __longlong_as_double(0x7ff8000000000000ll) : 0.0;
             const double *Ub = Us + (long long)n_begin * N;
 #pragma unroll
-            for (int j = 0; j < M; ++j) u[j] = (finite && node0 + j < N) ? __ldcg(Ub + j) : 0.0;
+            for (int j = 0; j < M; ++j) u[j] = (node0 + j < N) ? __ldcg(Ub + j) + poison : 0.0;
         }
         __syncwarp();
 
@@ -176,7 +179,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) fom_picard_kernel(const FomP
                 // ================= one Picard iteration (:667-698) ======================
                 const double uL = shfl_up(u[M - 1], 1), uR = shfl_down(u[0], 1);
                 double cs[M], rs[M], fs[M];
-                Continuant<M> ct;
+                Continuant<M, true> ct;
                 // element j = -1 (shared with the previous lane)
                 double offL, qL, GL;
                 {
@@ -184,7 +187,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) fom_picard_kernel(const FomP
                     const double sm = u1 + u2;
                     qL = fma(BX_A6L, u2, BX_A6L * sm);
                     const double z = fma(sm * (u2 - u1), 1.0 / 6.0, -w_hfs[lane]);
-                    GL = (BX_C1L * rcp(fmax(fabs(sm), 2.0e-10))) * z;
+                    GL = (BX_C1L * rcp1(fmax(fabs(sm), 2.0e-10))) * z;
                     offL = s_off[lane];
                 }
 #pragma unroll
@@ -199,7 +202,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) fom_picard_kernel(const FomP
                     double pe = fma(p.a6, u1, t6);
                     double qe = fma(p.a6, u2, t6);
                     const double z = fma(sm * (u2 - u1), 1.0 / 6.0, -w_hfs[ei]);
-                    double Ge = (p.c1 * rcp(fmax(fabs(sm), 2.0e-10))) * z;
+                    double Ge = (p.c1 * rcp1(fmax(fabs(sm), 2.0e-10))) * z;
                     if ((!EXACT || j == M - 1) && j == jl) { pe = 0.0; qe = 0.0; Ge = 0.0; }
                     const double off = s_off[ei];
                     // row j of A, b and r = -R = b - A U_k
@@ -262,10 +265,10 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) fom_picard_kernel(const FomP
         if (p.nseg > 1) {   // publish the segment: snapshot stores of all lanes, then the progress word
             __threadfence();
             __syncwarp();
-            if (lane == 0) {
-                const int word = finite ? reinterpret_cast<const int *>(w_mu1 + 1)[0] + 1 : -1;
-                asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p.progress + s), "r"(word) : "memory");
-            }
+            // every lane stores the same word (one transaction); a lane-0-only store here gets threaded into the
+            // lane-0-only atomicAdd at the top of the loop and costs the compiler its proof that the warp is
+            // converged at the shuffles (BRA.DIV before each of them, 100 bytes more spills: measured 5 % slower)
+            *reinterpret_cast<volatile int *>(p.progress + s) = finite ? reinterpret_cast<const int *>(w_mu1 + 1)[0] + 1 : -1;
         }
     }
 }
@@ -325,6 +328,21 @@ static int fom_warps_per_trajectory(int B, int N, int sms) {
 extern "C" long long bx_workspace_bytes(void) { return 256; }
 extern "C" long long bx_fom_workspace_bytes(int B) { return B < 0 ? BX_ERR_INVALID : 256 + 4LL * B; }
 
+// which kernel and how many warps per trajectory a sweep of B samples on N nodes gets on the current device:
+// returns 16 * kernel + warps (kernel 0 = throughput, 1 = latency), negative on error
+extern "C" int bx_fom_plan(int B, int N) {
+    using namespace bx;
+    BX_REQUIRE(B >= 0 && N >= 2 && N <= 1024, "bx_fom_plan: B >= 0 and 2 <= N <= 1024");
+    DeviceInfo di;
+    const int rc = device_info(di);
+    if (rc != BX_OK) return rc;
+    if (N > 128) {
+        const int forced = tuning(BX_TUNE_FOM_KERNEL);
+        if (forced >= 0 ? forced == 1 : (long long)B <= 8LL * di.sms) return 16 + fom_warps_per_trajectory(B, N, di.sms);
+    }
+    return 1;
+}
+
 extern "C" int bx_fom_picard_trajectories(int B, int N, int nsteps, const double *X, const double *u0,
                                           int u0_batched, const double *mu1, const double *mu2,
                                           double At, double E, double tol, int kmax, double *U,
@@ -352,10 +370,10 @@ extern "C" int bx_fom_picard_trajectories(int B, int N, int nsteps, const double
     const int rc = device_info(di);
     if (rc != BX_OK) return rc;
     // latency kernel (bx_fom_strong.cu) when the sweep cannot fill the warp slots of this one
-    if (!err_hist && N > 128) {
-        const int forced = tuning(BX_TUNE_FOM_KERNEL);
-        const bool strong = forced >= 0 ? forced == 1 : (long long)B <= 8LL * di.sms;
-        if (strong) return launch_fom_strong(p, fom_warps_per_trajectory(B, N, di.sms), st);
+    if (!err_hist) {
+        const int plan = bx_fom_plan(B, N);
+        if (plan < 0) return plan;
+        if (plan >= 16) return launch_fom_strong(p, plan & 15, st);
     }
     if (N <= 64) return launch_fom<2, 4, 4>(p, st);
     if (N <= 128) return launch_fom<4, 4, 4>(p, st);

@@ -186,14 +186,14 @@ __global__ void __launch_bounds__(32 * W, StrongShape<M, W>::MINB) fom_strong_ke
         // front half of a Picard iteration: assembly of A, b, r = b - A U_k from the current iterate and the
         // lane-local continuant Thomas sweep (:667-692)
         auto front = [&]() {
-            Continuant<M> ct;
+            Continuant<M, true> ct;
             double offL, qL, GL;
             {
                 const double u1 = uL, u2 = u[0];
                 const double sm = u1 + u2;
                 qL = fma(a6L, u2, a6L * sm);
                 const double z = fma(sm * (u2 - u1), 1.0 / 6.0, -w_hfs[gl]);
-                GL = (c1L * rcp(fmax(fabs(sm), 2.0e-10))) * z;
+                GL = (c1L * rcp1(fmax(fabs(sm), 2.0e-10))) * z;
                 offL = s_off[gl];
             }
 #pragma unroll
@@ -207,7 +207,7 @@ __global__ void __launch_bounds__(32 * W, StrongShape<M, W>::MINB) fom_strong_ke
                 double pe = fma(a6, u1, t);
                 double qe = fma(a6, u2, t);
                 const double z = fma(sm * (u2 - u1), 1.0 / 6.0, -w_hfs[ei]);
-                double Ge = (c1 * rcp(fmax(fabs(sm), 2.0e-10))) * z;
+                double Ge = (c1 * rcp1(fmax(fabs(sm), 2.0e-10))) * z;
                 if ((!EXACT || j == M - 1) && j == jl) { pe = 0.0; qe = 0.0; Ge = 0.0; }
                 const double off = s_off[ei];
                 double a = offL - qL;
@@ -223,7 +223,7 @@ __global__ void __launch_bounds__(32 * W, StrongShape<M, W>::MINB) fom_strong_ke
 
         int n = 0;
         bool finite = true;
-        for (; n < p.nsteps; ++n) {
+        for (; finite && n < p.nsteps; ++n) {
             // ---- bn = M U^n + At F (constant during the Picard loop, :683) ---------------------------
             {
                 double h6L = s_h6[gl];
@@ -242,7 +242,6 @@ __global__ void __launch_bounds__(32 * W, StrongShape<M, W>::MINB) fom_strong_ke
             for (;;) {
                 double xl, P;
                 if constexpr (W == 1) {
-                    if (k > 0 && (!(sd > p.tol2 * su) || k >= p.kmax)) break;
                     {
                         double F, G, R;
                         partition_upward<M>(cs, rs, fs, F, G, R);
@@ -343,6 +342,9 @@ __global__ void __launch_bounds__(32 * W, StrongShape<M, W>::MINB) fom_strong_ke
                 sd = d0 + d1; su = n0 + n1;
                 warp_sum2(sd, su, lane);
                 front();
+                if constexpr (W == 1) {   // (W > 1 decides behind the barrier that carries the next condensed rows)
+                    if (!(sd > p.tol2 * su) || k >= p.kmax) break;
+                }
             }
 
             // ---- snapshot n+1 (:705) and iteration count -------------------------------------------
@@ -356,7 +358,6 @@ __global__ void __launch_bounds__(32 * W, StrongShape<M, W>::MINB) fom_strong_ke
             }
             finite = su <= 1.7976931348623157e308;   // false for inf and NaN
             if (gl == 0 && p.iters) p.iters[(long long)s * p.nsteps + n] = finite ? k : -1;
-            if (!finite) { ++n; break; }
         }
         if (!finite) {   // as bx_fom.cu: flag -1 and NaN snapshots from the first non-finite step on
             const double qnan = __longlong_as_double(0x7ff8000000000000ll);

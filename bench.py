@@ -322,7 +322,7 @@ class Bench:
         iters_all = self.reduce(total_iters, "sum")
         value = args.samples * nT * args.steps / (total_ms * 1e-3)
         lib = self.bx._lib.load()
-        W_used = self.fom_variant(B)
+        kern_used, W_used = self.fom_variant(B)
 
         # ---- weak leg (round-1 definition), N > 1 only --------------------------------------------
         weak = None
@@ -359,7 +359,7 @@ class Bench:
         # ---- roofline of the dominant (only) kernel of the headline --------------------------------------
         hbm_peak, hbm_src = measured_peak_hbm()
         k_ms = float(np.mean(per_launch_ms))
-        variant = f"fom_w{W_used}"
+        variant = f"fom_{kern_used}_w{W_used}"
         cap_ = ncu_capture(variant) or {}
         instr = cap_.get("fp64_warp_instructions_per_picard_iteration")
         model_bytes = 88.0 * N_NODES * total_iters + 8.0 * N_NODES * B * nT     # SURVEY 8(d), this rank's launch
@@ -378,7 +378,9 @@ class Bench:
             "traffic_source": (f"ncu --set full dram__bytes_read.sum + dram__bytes_write.sum, captured on {cap_.get('capture')}"
                                if same_cfg else "null: the committed capture is for another samples/nsteps"),
             "fp64_pipe_active_pct_ncu": cap_.get("fp64_pipe_active_pct") if same_cfg else None,
-            "kernel": f"bx::fom_picard_kernel ({W_used} warp(s) per trajectory)", "kernel_ms": k_ms,
+            "kernel": (f"bx::fom_picard_kernel (throughput instance, one warp per trajectory, round-robin segments)"
+                       if kern_used == "throughput" else f"bx::fom_strong_kernel (latency instance, {W_used} warp(s) per trajectory)"),
+            "kernel_ms": k_ms,
             "picard_iterations_per_launch": total_iters,
             "model_frac": model_gbs / hbm_peak, "model_gbs": model_gbs, "model_peak_gbs": hbm_peak, "model_peak_source": hbm_src,
             "model": "banded-dataflow equivalent of SURVEY 8d: 88*N B per Picard iteration + 8*N B per time step per sample; the "
@@ -401,7 +403,7 @@ class Bench:
                 "trajectories_per_s": args.samples * args.steps / (total_ms * 1e-3),
                 "picard_iterations_per_s": iters_all * args.steps / (total_ms * 1e-3),
                 "strong": {"value": value, "unit": UNIT, "ms_per_step": total_ms / args.steps, "samples_total": args.samples,
-                           "warps_per_trajectory": W_used},
+                           "kernel": kern_used, "warps_per_trajectory": W_used},
                 "weak": weak, "roofline": roofline,
                 "fp64_peaks_measured": {"dfma_tflops": dfma_peak, "dmma_tflops": dmma_peak},
                 "extra_workloads": extra, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
@@ -411,12 +413,11 @@ class Bench:
             self.dist.destroy_process_group()
 
     def fom_variant(self, B):
-        """Warps per trajectory the library picks for B samples (mirrors fom_warps_per_trajectory in csrc/bx_fom.cu)."""
-        forced = self.bx.get_tuning("fom_warps_per_trajectory")
-        if forced in (1, 2, 4):
-            return forced
-        sms = self.bx._lib.load().bx_device_sm_count()
-        return 4 if B <= 2 * sms else 2 if B <= 6 * sms else 1
+        """(kernel, warps per trajectory) the library picks for B samples of 512 nodes: bx_fom_plan."""
+        plan = self.bx._lib.load().bx_fom_plan(int(B), N_NODES)
+        if plan < 0:
+            raise RuntimeError("bx_fom_plan failed")
+        return ("latency" if plan >= 16 else "throughput"), plan & 15
 
     # -- e2e ------------------------------------------------------------------------------------------
     def e2e_leg(self, m1, m2, B, nT):

@@ -122,6 +122,9 @@ long long bx_workspace_bytes(void);
  * (BX_TUNE_FOM_KERNEL / BX_TUNE_FOM_WARPS_PER_TRAJECTORY force the choice).
  * workspace: bx_fom_workspace_bytes(B) bytes (contents ignored, overwritten).             */
 long long bx_fom_workspace_bytes(int B);
+/* the launch a sweep of B samples on N nodes gets on the current device: 16 * kernel + warps per trajectory
+ * (kernel 0 = throughput kernel, 1 = latency kernel); negative = error code                            */
+int bx_fom_plan(int B, int N);
 int bx_fom_picard_trajectories(int B, int N, int nsteps, const double *X, const double *u0,
                                int u0_batched, const double *mu1, const double *mu2,
                                double At, double E, double tol, int kmax,

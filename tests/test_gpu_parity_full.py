@@ -57,6 +57,23 @@ def test_qm_config4_path_vs_oracle(n, proj, oracle, fem512, training_snapshots):
     X, _ = oracle.mesh(512)
     Phi, H = _manifold(oracle, training_snapshots, n)
     nT = 12
+    # The reduced Gauss-Newton / Galerkin system gets worse conditioned with every mode added (n = 31 Galerkin:
+    # kappa ~ 1e9), so FP64 itself does not pin the trajectory to 1e-10 there: the oracle run again with Phi and H
+    # moved by ONE ulp (an equally valid FP64 statement of the same problem) gives this problem's own rounding
+    # sensitivity `sens`; the kernel is held to max(1e-10, 20 * sens) - 1e-10 wherever the problem allows it
+    # (n = 24 and 28 do), never looser than twenty one-ulp perturbations.
+    rng = np.random.default_rng(n)
+    Phi1 = np.nextafter(Phi, Phi + np.where(rng.random(Phi.shape) < 0.5, -1.0, 1.0))
+    H1 = np.nextafter(H, H + np.where(rng.random(H.shape) < 0.5, -1.0, 1.0))
+    sens = 0.0
+    for b in range(3):
+        Ua, _ = oracle.pod_quadratic_manifold(X, 0.05, nT, np.ones(512), QM_MU1[b], 0.0, QM_MU2[b], Phi, H, proj)
+        Ub, _ = oracle.pod_quadratic_manifold(X, 0.05, nT, np.ones(512), QM_MU1[b], 0.0, QM_MU2[b], Phi1, H1, proj)
+        sens = max(sens, rel_l2_per_step(Ub, Ua))
+    tol = max(TOL, 20.0 * sens)
+    assert tol <= 1e-6, f"one-ulp sensitivity {sens:.1e}: the case is too ill-conditioned to test anything"
+    if n <= 28:
+        assert tol == TOL, f"n = {n}: the 1e-10 bar must hold as is (sens = {sens:.1e})"
     # two passes: the reference's default cap (25, never reached here: the first step needs 18 at most) and a cap of 6,
     # which the first steps of every sample reach (the ':1171' non-convergence branch of the reference)
     for itmax in (25, 6):
@@ -74,7 +91,7 @@ def test_qm_config4_path_vs_oracle(n, proj, oracle, fem512, training_snapshots):
                 burgers_b200.set_tuning("qm_schedule", -1)
             for b, (Uo, ito) in enumerate(ref):
                 assert np.array_equal(it[b], ito), (itmax, sched, b, it[b], ito)
-                assert rel_l2_per_step(U[b].T, Uo) <= TOL, (itmax, sched, b)
+                assert rel_l2_per_step(U[b].T, Uo) <= tol, (itmax, sched, b, sens)
 
 
 @pytest.mark.parametrize("proj", ["Galerkin", "LSPG"])
