@@ -62,8 +62,15 @@ int kernel_occupancy(const void *kern, int threads, size_t smem, int *occ_out) {
             if (occ_out) *occ_out = e.occ;
             return BX_OK;
         }
-    // the attribute is per function and monotone here: only ever raise the opt-in size
-    BX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    // the opt-in size is ONE attribute per (function, device): only ever raise it, or a launch shape cached earlier
+    // with a larger size would be launched against a lowered limit
+    {
+        size_t have = 0;
+        for (const Key &e : cache)
+            if (e.k == kern && e.dev == dev && e.smem > have) have = e.smem;
+        if (smem > have)
+            BX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    }
     int occ = 0;
     BX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, threads, smem));
     cache.push_back(Key{kern, dev, threads, smem, occ});

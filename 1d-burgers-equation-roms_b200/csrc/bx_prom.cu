@@ -417,7 +417,12 @@ static int launch_prom_t(PromParams p, int min_warps, cudaStream_t st, bool *fit
     if (warps > PROM_MAXW) warps = PROM_MAXW;
     *fits = warps >= min_warps;
     if (!*fits) return BX_OK;
-    if (warps > p.B) warps = p.B;
+    // a sweep smaller than the device (strong scaling: 512 samples per GPU) spreads over ALL SMs first: as many
+    // warps per CTA as it takes to seat B trajectories on `sms` CTAs, not full CTAs on a fraction of the SMs
+    {
+        const long long per_sm = ((long long)p.B + sms - 1) / sms;
+        if (warps > per_sm) warps = per_sm < 1 ? 1 : per_sm;
+    }
     p.warps = (int)warps;
     const size_t smem = sizeof(double) * ((size_t)lay.per_cta + (size_t)warps * lay.per_warp);
     auto kern = prom_kernel<NB, LSPG, PHIS>;

@@ -33,6 +33,7 @@ namespace bx {
 
 struct QmParams {
     int B, N, n, k, nsteps, itmax, warps;
+    int group;           // trajectories a CTA integrates in lock step (<= QM_MAXW; fewer when the sweep is smaller than the device)
     const double *X;
     const double *u0;
     long long u0_stride;
@@ -281,10 +282,10 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel(const QmParams p) {
     __shared__ int s_base;
     for (;;) {
         __syncthreads();
-        if (threadIdx.x == 0) s_base = (int)atomicAdd(p.counter, (unsigned)QM_MAXW);
+        if (threadIdx.x == 0) s_base = (int)atomicAdd(p.counter, (unsigned)p.group);
         __syncthreads();
         if (s_base >= p.B) break;
-        const bool active = s_base + warp < p.B;          // a ragged last group runs idle warps (q = 0)
+        const bool active = warp < p.group && s_base + warp < p.B;   // idle warps (ragged last group, small groups) carry q = 0
         const int smp = active ? s_base + warp : p.B - 1;
         rc.mu1 = p.mu1[smp];
         const double *atf = p.atf + (size_t)smp * N;
@@ -597,10 +598,10 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel_ts(const QmParams p
     __shared__ int s_base;
     for (;;) {
         __syncthreads();
-        if (threadIdx.x == 0) s_base = (int)atomicAdd(p.counter, (unsigned)QM_MAXW);
+        if (threadIdx.x == 0) s_base = (int)atomicAdd(p.counter, (unsigned)p.group);
         __syncthreads();
         if (s_base >= p.B) break;
-        const bool active = s_base + warp < p.B;
+        const bool active = warp < p.group && s_base + warp < p.B;
         const int smp = active ? s_base + warp : p.B - 1;
         rc.mu1 = p.mu1[smp];
         const double *atf = p.atf + (size_t)smp * N;
@@ -845,8 +846,17 @@ static int launch_qm_t(QmParams p, const QmPlan &pl, const double *H, cudaStream
         const int rco = kernel_occupancy(reinterpret_cast<const void *>(kern), (int)warps * 32, smem, nullptr);
         if (rco != BX_OK) return rco;
     }
+    // a sweep smaller than the device (strong scaling: 512 samples per GPU) spreads over ALL SMs: lock-step groups of
+    // ceil(B / SMs) trajectories instead of full groups of eight on a fraction of the SMs (the idle rows of the
+    // tangent DMMA cost nothing there: the SM would otherwise be empty)
+    {
+        const long long per_sm = ((long long)p.B + pl.sms - 1) / pl.sms;
+        p.group = (int)(per_sm < 1 ? 1 : per_sm > QM_MAXW ? QM_MAXW : per_sm);
+        const int f = tuning(BX_TUNE_QM_GROUP);
+        if (f >= 1 && f <= QM_MAXW) p.group = f;
+    }
     long long ctas = pl.sms;
-    const long long need = ((long long)p.B + warps - 1) / warps;
+    const long long need = ((long long)p.B + p.group - 1) / p.group;
     if (ctas > need) ctas = need;
     BX_CUDA(cudaMemsetAsync(p.counter, 0, sizeof(unsigned int), st));
     const long long work = (long long)p.N * NB * 32 * 2 * NB + (long long)p.B * p.N;
