@@ -47,6 +47,8 @@ struct PromParams {
     int *iters;
     double *err_hist;    // optional (B, nsteps, kmax): |dq| / |q| after every iteration (:776)
     unsigned int *counter;
+    int *progress;       // workspace: (B,) segments completed per trajectory (-1: not finite any more); nseg > 1 only
+    int nseg, seg;       // the nsteps time steps are cut into nseg segments of seg steps, handed out round-robin
 };
 
 constexpr int PROM_MAXW = 8;
@@ -182,26 +184,44 @@ __global__ void __launch_bounds__(PROM_MAXW * 32, 1) prom_kernel(const PromParam
     rc.a6 = At / 6.0; rc.c1 = 1.5 * At; rc.ate = At * p.E; rc.has_e = p.E != 0.0; rc.supg = true;
     rc.N = N; rc.S = S; rc.lgS = lgS;
 
+    // Work units are SEGMENTS of trajectories, handed out round-robin (unit = segment * B + sample) so that all
+    // trajectories advance together and every warp slot stays busy until the last segment; a trajectory resumes from
+    // its own last snapshot, gated by a progress word (same scheme as the FOM sweep, csrc/bx_fom.cu).
     for (;;) {
-        int smp = 0;
-        if (lane == 0) smp = (int)atomicAdd(p.counter, 1u);
-        smp = __shfl_sync(FULL, smp, 0);
-        if (smp >= p.B) break;
+        unsigned unit = 0;
+        if (lane == 0) unit = atomicAdd(p.counter, 1u);
+        unit = __shfl_sync(FULL, unit, 0);
+        if (unit >= (unsigned)p.B * (unsigned)p.nseg) break;
+        const int sg = (int)(unit / (unsigned)p.B);
+        const int smp = (int)(unit - (unsigned)sg * (unsigned)p.B);
+        const int n_begin = sg * p.seg;
+        const int n_end = min(p.nsteps, n_begin + p.seg);
         rc.mu1 = p.mu1[smp];
         const double *atf = p.atf + (size_t)smp * N;
 
-        // ---- per-sample forcing constants and the initial condition ---------------------
+        // ---- per-sample forcing constants and the state at the start of the segment ------
         double *Us = p.U + (long long)smp * (long long)(p.nsteps + 1) * N;
         {
             const double *hf = p.hfs + (size_t)smp * N;
-            const double *u0p = p.u0 + (long long)smp * p.u0_stride;
+            const double *src = p.u0 + (long long)smp * p.u0_stride;
+            double poison = 0.0;
+            if (sg > 0) {   // every lane polls the same word (see csrc/bx_fom.cu for why not lane 0 alone)
+                int done;
+                const volatile int *flag = p.progress + smp;
+                while ((done = *flag) < sg && done >= 0) __nanosleep(500);
+                done = __shfl_sync(FULL, done, 0);
+                __threadfence();
+                // a trajectory that stopped being finite earlier is poisoned as data: its first step here takes the flag
+                if (done < 0) poison = __longlong_as_double(0x7ff8000000000000ll);
+                src = Us + (long long)n_begin * N;
+            }
             for (int i = lane - 1; i <= NP; i += 32) {
                 const int o = sk(i, S, lgS);
                 w_hfs[o] = (i >= 0 && i <= N - 2) ? hf[i] : 0.0;
-                const double v = (i >= 0 && i < N) ? u0p[i] : 0.0;
+                const double v = (i >= 0 && i < N) ? __ldcg(src + i) + poison : 0.0;
                 w_u[o] = v;
                 w_bn[o] = 0.0;
-                if (i >= 0 && i < N) Us[i] = v;
+                if (sg == 0 && i >= 0 && i < N) Us[i] = v;
             }
         }
         __syncwarp();
@@ -219,7 +239,8 @@ __global__ void __launch_bounds__(PROM_MAXW * 32, 1) prom_kernel(const PromParam
             q0 = lane < n ? (q4[0] + q4[1]) + (q4[2] + q4[3]) : 0.0;
         }
 
-        for (int step = 0; step < p.nsteps; ++step) {
+        bool bad = false;
+        for (int step = n_begin; step < n_end; ++step) {
             // ---- bn = M U^n + At F (:745), constant during the nonlinear loop ------------
             for (int i = lane; i < N; i += 32) {
                 const double h6L = s_h6[sk(i - 1, S, lgS)], h6R = s_h6[sk(i, S, lgS)];
@@ -391,12 +412,18 @@ __global__ void __launch_bounds__(PROM_MAXW * 32, 1) prom_kernel(const PromParam
             if (lane == 0 && p.iters) p.iters[(long long)smp * p.nsteps + step] = finite ? k : -1;
             if (!finite) {   // singular reduced system / overflow (np.linalg.LinAlgError at :767): flag -1 and NaN
                 const double qnan = __longlong_as_double(0x7ff8000000000000ll);   // snapshots from here on, batch goes on
-                for (++step; step < p.nsteps; ++step) {
+                for (++step; step < n_end; ++step) {
                     double *Un2 = Us + (long long)(step + 1) * N;
                     for (int i = lane; i < N; i += 32) Un2[i] = qnan;
                     if (lane == 0 && p.iters) p.iters[(long long)smp * p.nsteps + step] = -1;
                 }
+                bad = true;
             }
+        }
+        if (p.nseg > 1) {   // publish the segment: the snapshot stores of all lanes, then the progress word (all lanes)
+            __threadfence();
+            __syncwarp();
+            *reinterpret_cast<volatile int *>(p.progress + smp) = bad ? -1 : sg + 1;
         }
         __syncwarp();
     }
@@ -432,8 +459,17 @@ static int launch_prom_t(PromParams p, int min_warps, cudaStream_t st, bool *fit
     }
     long long ctas = sms;
     const long long need = ((long long)p.B + warps - 1) / warps;
-    if (ctas > need) ctas = need;
+    p.nseg = 1; p.seg = p.nsteps > 0 ? p.nsteps : 1;
+    if (ctas >= need) {
+        ctas = need;
+    } else if (!p.err_hist) {   // more trajectories than warp slots: round-robin segments
+        int seg = tuning(BX_TUNE_FOM_SEGMENT_STEPS);
+        if (seg < 0) seg = 25;
+        if (seg > 0 && seg < p.nsteps) { p.seg = seg; p.nseg = (p.nsteps + seg - 1) / seg; }
+    }
+    BX_REQUIRE((long long)p.B * p.nseg < 0xffffffffLL, "too many work units (B = %d, %d segments)", p.B, p.nseg);
     BX_CUDA(cudaMemsetAsync(p.counter, 0, sizeof(unsigned int), st));
+    if (p.nseg > 1) BX_CUDA(cudaMemsetAsync(p.progress, 0, sizeof(int) * (size_t)p.B, st));
     prom_forcing_kernel<<<(unsigned)(((long long)p.B * p.N + 255) / 256), 256, 0, st>>>(p.B, p.N, p.X, p.mu2, p.At,
                                                                                         p.atf, p.hfs);
     BX_LAUNCH_CHECK();
@@ -466,8 +502,9 @@ static int launch_prom(const PromParams &p, cudaStream_t st) {
 
 }  // namespace bx
 
+// 256-byte head | At F (B, N) | (h/6)(f1 + f2) (B, N) | progress words (B,)
 static long long prom_forcing_bytes(int B, int N) {
-    return (256 + 2LL * (long long)B * (long long)N * (long long)sizeof(double) + 15) & ~15LL;
+    return (256 + 2LL * (long long)B * (long long)N * (long long)sizeof(double) + 4LL * B + 15) & ~15LL;
 }
 
 extern "C" long long bx_prom_workspace_bytes(int B, int N, int n) {
@@ -519,6 +556,8 @@ extern "C" int bx_prom_trajectories(int B, int N, int n, int nsteps, const doubl
     p.counter = queue_slot(workspace);
     p.atf = reinterpret_cast<double *>(static_cast<char *>(workspace) + 256);
     p.hfs = p.atf + (size_t)B * N;
+    p.progress = reinterpret_cast<int *>(p.hfs + (size_t)B * N);
+    p.nseg = 1; p.seg = nsteps > 0 ? nsteps : 1;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     return projection == BX_LSPG ? launch_prom<true>(p, st) : launch_prom<false>(p, st);
 }

@@ -33,6 +33,8 @@ namespace bx {
 
 struct QmParams {
     int B, N, n, k, nsteps, itmax, warps;
+    int ngroups, nseg, seg;   // B / group lock-step groups; the time steps are cut into nseg segments of seg steps (round-robin units)
+    int *progress;       // workspace: (ngroups,) segments completed per group
     int group;           // trajectories a CTA integrates in lock step (<= QM_MAXW; fewer when the sweep is smaller than the device)
     const double *X;
     const double *u0;
@@ -279,32 +281,56 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel(const QmParams p) {
         __syncthreads();   // T rows (global) and u (shared) of all trajectories written
     };
 
-    __shared__ int s_base;
+    __shared__ int s_base, s_seg;
     for (;;) {
         __syncthreads();
-        if (threadIdx.x == 0) s_base = (int)atomicAdd(p.counter, (unsigned)p.group);
+        // work unit = (segment of time steps, lock-step group), handed out round-robin so that all groups advance
+        // together (same scheme as the FOM sweep, csrc/bx_fom.cu); a group resumes from its own last snapshots
+        if (threadIdx.x == 0) {
+            const unsigned unit = atomicAdd(p.counter, 1u);
+            int sgv = -1;
+            if (unit < (unsigned)p.ngroups * (unsigned)p.nseg) {
+                sgv = (int)(unit / (unsigned)p.ngroups);
+                const int gi = (int)(unit - (unsigned)sgv * (unsigned)p.ngroups);
+                if (sgv > 0) {
+                    const volatile int *flag = p.progress + gi;
+                    while (*flag < sgv) __nanosleep(500);
+                    __threadfence();
+                }
+                s_base = gi * p.group;
+            }
+            s_seg = sgv;
+        }
         __syncthreads();
-        if (s_base >= p.B) break;
+        if (s_seg < 0) break;
+        const int sg = s_seg;
+        const int n_begin = sg * p.seg;
+        const int n_end = min(p.nsteps, n_begin + p.seg);
         const bool active = warp < p.group && s_base + warp < p.B;   // idle warps (ragged last group, small groups) carry q = 0
         const int smp = active ? s_base + warp : p.B - 1;
         rc.mu1 = p.mu1[smp];
         const double *atf = p.atf + (size_t)smp * N;
 
         double *Us = p.U + (long long)smp * (long long)(p.nsteps + 1) * N;
+        bool bad = false;   // this warp's trajectory stopped being finite
         {
-            const double *u0p = p.u0 + (long long)smp * p.u0_stride;
+            const double *u0p = sg == 0 ? p.u0 + (long long)smp * p.u0_stride : Us + (long long)n_begin * N;
+            bool nan_seen = false;
             for (int i = lane - 1; i <= NP; i += 32) {
                 const int o = sk(i, S, lgS);
-                const double v = (active && i >= 0 && i < N) ? u0p[i] : 0.0;
+                const double v = (active && i >= 0 && i < N) ? __ldcg(u0p + i) : 0.0;
+                nan_seen |= v != v;
                 w_u[o] = v;
                 w_bn[o] = 0.0;
-                if (active && i >= 0 && i < N) Us[i] = v;
+                if (sg == 0 && active && i >= 0 && i < N) Us[i] = v;
             }
+            bad = sg > 0 && __any_sync(FULL, nan_seen);   // a trajectory flagged in an earlier segment left NaN snapshots
+            if (bad)
+                for (int i = lane - 1; i <= NP; i += 32) w_u[sk(i, S, lgS)] = 0.0;
         }
         __syncwarp();
-        bool bad = false;   // this warp's trajectory stopped being finite
 
-        for (int step = 0; step < p.nsteps; ++step) {
+        for (int step = n_begin; step < n_end; ++step) {
             // ---- bn = M U^m + At F (:1140) and the initial guess q = Phi^T U^m (:1129) --------
             for (int i = lane; i < N; i += 32) {
                 const double h6L = s_h6[sk(i - 1, S, lgS)], h6R = s_h6[sk(i, S, lgS)];
@@ -435,6 +461,11 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel(const QmParams p) {
                 for (int i = lane; i < N; i += 32) Un1[i] = bad ? qnan : w_u[sk(i, S, lgS)];
                 if (lane == 0 && p.iters) p.iters[(long long)smp * p.nsteps + step] = bad ? -1 : it_done;
             }
+        }
+        if (p.nseg > 1) {   // publish the segment: every thread's snapshot stores, then the group's progress word
+            __threadfence();
+            __syncthreads();
+            if (threadIdx.x == 0) *reinterpret_cast<volatile int *>(p.progress + s_base / p.group) = sg + 1;
         }
     }
 }
@@ -595,31 +626,55 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel_ts(const QmParams p
         }
     };
 
-    __shared__ int s_base;
+    __shared__ int s_base, s_seg;
     for (;;) {
         __syncthreads();
-        if (threadIdx.x == 0) s_base = (int)atomicAdd(p.counter, (unsigned)p.group);
+        // work unit = (segment of time steps, lock-step group), handed out round-robin so that all groups advance
+        // together (same scheme as the FOM sweep, csrc/bx_fom.cu); a group resumes from its own last snapshots
+        if (threadIdx.x == 0) {
+            const unsigned unit = atomicAdd(p.counter, 1u);
+            int sgv = -1;
+            if (unit < (unsigned)p.ngroups * (unsigned)p.nseg) {
+                sgv = (int)(unit / (unsigned)p.ngroups);
+                const int gi = (int)(unit - (unsigned)sgv * (unsigned)p.ngroups);
+                if (sgv > 0) {
+                    const volatile int *flag = p.progress + gi;
+                    while (*flag < sgv) __nanosleep(500);
+                    __threadfence();
+                }
+                s_base = gi * p.group;
+            }
+            s_seg = sgv;
+        }
         __syncthreads();
-        if (s_base >= p.B) break;
-        const bool active = warp < p.group && s_base + warp < p.B;
+        if (s_seg < 0) break;
+        const int sg = s_seg;
+        const int n_begin = sg * p.seg;
+        const int n_end = min(p.nsteps, n_begin + p.seg);
+        const bool active = warp < p.group && s_base + warp < p.B;   // idle warps (ragged last group, small groups) carry q = 0
         const int smp = active ? s_base + warp : p.B - 1;
         rc.mu1 = p.mu1[smp];
         const double *atf = p.atf + (size_t)smp * N;
         double *Us = p.U + (long long)smp * (long long)(p.nsteps + 1) * N;
+        bool bad = false;   // this warp's trajectory stopped being finite
         {
-            const double *u0p = p.u0 + (long long)smp * p.u0_stride;
+            const double *u0p = sg == 0 ? p.u0 + (long long)smp * p.u0_stride : Us + (long long)n_begin * N;
+            bool nan_seen = false;
             for (int i = lane - 1; i <= NP; i += 32) {
                 const int o = sk(i, S, lgS);
-                const double v = (active && i >= 0 && i < N) ? u0p[i] : 0.0;
+                const double v = (active && i >= 0 && i < N) ? __ldcg(u0p + i) : 0.0;
+                nan_seen |= v != v;
                 w_u[o] = v;
                 w_bn[o] = 0.0;
-                if (active && i >= 0 && i < N) Us[i] = v;
+                if (sg == 0 && active && i >= 0 && i < N) Us[i] = v;
             }
+            bad = sg > 0 && __any_sync(FULL, nan_seen);   // a trajectory flagged in an earlier segment left NaN snapshots
+            if (bad)
+                for (int i = lane - 1; i <= NP; i += 32) w_u[sk(i, S, lgS)] = 0.0;
         }
         __syncwarp();
-        bool bad = false;   // this warp's trajectory stopped being finite
 
-        for (int step = 0; step < p.nsteps; ++step) {
+        for (int step = n_begin; step < n_end; ++step) {
             for (int i = lane; i < N; i += 32) {
                 const double h6L = s_h6[sk(i - 1, S, lgS)], h6R = s_h6[sk(i, S, lgS)];
                 const double um = w_u[sk(i - 1, S, lgS)], uc = w_u[sk(i, S, lgS)], up = w_u[sk(i + 1, S, lgS)];
@@ -786,12 +841,17 @@ __global__ void __launch_bounds__(QM_MAXW * 32, 1) qm_kernel_ts(const QmParams p
                 if (lane == 0 && p.iters) p.iters[(long long)smp * p.nsteps + step] = bad ? -1 : it_done;
             }
         }
+        if (p.nseg > 1) {   // publish the segment: every thread's snapshot stores, then the group's progress word
+            __threadfence();
+            __syncthreads();
+            if (threadIdx.x == 0) *reinterpret_cast<volatile int *>(p.progress + s_base / p.group) = sg + 1;
+        }
     }
 }
 
 struct QmPlan {
     int sms, maxsm, NP, NB;
-    size_t off_hs, off_atf, off_tg, total;
+    size_t off_hs, off_atf, off_tg, off_prog, total;
 };
 
 static int qm_plan(int B, int N, int n, QmPlan &pl) {
@@ -809,6 +869,8 @@ static int qm_plan(int B, int N, int n, QmPlan &pl) {
     pl.off_hs = o; o += sizeof(double) * (size_t)N * pl.NB * 32 * 2 * pl.NB; o = (o + 255) & ~(size_t)255;
     pl.off_atf = o; o += sizeof(double) * (size_t)B * N; o = (o + 255) & ~(size_t)255;
     pl.off_tg = o; o += sizeof(double) * (size_t)pl.sms * QM_MAXW * (size_t)(pl.NP + 2 + QM_PF) * 32;
+    o = (o + 255) & ~(size_t)255;
+    pl.off_prog = o; o += sizeof(int) * (size_t)(B > 0 ? B : 1);
     pl.total = o;
     return BX_OK;
 }
@@ -857,8 +919,17 @@ static int launch_qm_t(QmParams p, const QmPlan &pl, const double *H, cudaStream
     }
     long long ctas = pl.sms;
     const long long need = ((long long)p.B + p.group - 1) / p.group;
-    if (ctas > need) ctas = need;
+    p.ngroups = (int)need;
+    p.nseg = 1; p.seg = p.nsteps > 0 ? p.nsteps : 1;
+    if (ctas >= need) {
+        ctas = need;
+    } else if (!p.err_hist) {   // more groups than SMs: round-robin segments of time steps
+        int seg = tuning(BX_TUNE_FOM_SEGMENT_STEPS);
+        if (seg < 0) seg = 25;
+        if (seg > 0 && seg < p.nsteps) { p.seg = seg; p.nseg = (p.nsteps + seg - 1) / seg; }
+    }
     BX_CUDA(cudaMemsetAsync(p.counter, 0, sizeof(unsigned int), st));
+    if (p.nseg > 1) BX_CUDA(cudaMemsetAsync(p.progress, 0, sizeof(int) * (size_t)p.ngroups, st));
     const long long work = (long long)p.N * NB * 32 * 2 * NB + (long long)p.B * p.N;
     qm_prep_kernel<<<(unsigned)((work + 255) / 256), 256, 0, st>>>(p.B, p.N, NB, p.n, p.k, p.X, p.mu2, p.At, H,
                                                                  const_cast<double *>(p.Hs), p.atf);
@@ -928,6 +999,7 @@ extern "C" int bx_qm_prom_trajectories(int B, int N, int n, int nsteps, const do
     p.Hs = reinterpret_cast<double *>(ws + pl.off_hs);
     p.atf = reinterpret_cast<double *>(ws + pl.off_atf);
     p.Tg = reinterpret_cast<double *>(ws + pl.off_tg);
+    p.progress = reinterpret_cast<int *>(ws + pl.off_prog);
     p.U = U; p.iters = iters; p.err_hist = err_hist;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     return projection == BX_LSPG ? launch_qm<true>(p, pl, H, st) : launch_qm<false>(p, pl, H, st);

@@ -62,7 +62,7 @@ int         bx_device_sm_count(void);
                                                0 global scratch, 1 shared-memory tile, 2 chunked global   */
 #define BX_TUNE_PROM_WARPS_PER_TRAJECTORY 4 /* 1 or 2 warps integrate one POD-PROM trajectory (n <= 31)   */
 #define BX_TUNE_FOM_KERNEL               5  /* 0 throughput kernel, 1 latency kernel (speculative front half) */
-#define BX_TUNE_FOM_SEGMENT_STEPS        6  /* time steps per work unit of the throughput kernel (0: whole trajectories) */
+#define BX_TUNE_FOM_SEGMENT_STEPS        6  /* time steps per round-robin work unit of the FOM / POD-PROM / quadratic-manifold sweeps (0: whole trajectories) */
 #define BX_TUNE_QM_GROUP                 7  /* 1 .. 8 trajectories per lock-step group of the quadratic-manifold PROM */
 #define BX_TUNE_COUNT                    8
 int bx_set_tuning(int knob, int value);

@@ -70,3 +70,74 @@ def test_segmented_sweep_nonfinite_trajectory_keeps_its_flag(oracle, tuning):
     good = np.setdiff1d(np.arange(B), bad)
     assert (it[good] > 0).all() and np.isfinite(Uc[good]).all()
     assert (it[good] == it[good[0]]).all() and (Uc[good] == Uc[good[0]]).all()
+
+
+def _phi(n):
+    from conftest import GOLDEN
+    return np.ascontiguousarray(np.load(f"{GOLDEN}/Phi_tol_1e-04.npy")[:, :n])
+
+
+@pytest.mark.parametrize("proj", ["LSPG", "Galerkin"])
+def test_prom_segmented_sweep_matches_whole_trajectories(proj, oracle, tuning):
+    """POD-PROM warp kernel (csrc/bx_prom.cu) with more trajectories than warp slots: round-robin segments against whole
+    trajectories from the queue.  A resumed trajectory projects its snapshot explicitly (q0 = Phi^T U, as the reference
+    does at :770) where the running one uses (Phi^T Phi) q, so the two agree to rounding, not bit for bit: 1e-12 per
+    step and identical counts; both against the oracle on a strided sample."""
+    import burgers_b200
+    X, _ = oracle.mesh(512)
+    fem = burgers_b200.FEMBurgers(X)
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    B = 8 * sms + 150
+    rng = np.random.default_rng(7)
+    mu1 = 4.25 + 1.25 * rng.random(B); mu2 = 0.015 + 0.015 * rng.random(B)
+    Phi = _phi(28)
+    nT = 11
+    tuning("fom_segment_steps", 0)
+    U0, it0 = fem.pod_prom_burgers_batch(0.05, nT, np.ones(512), mu1, 0.0, mu2, Phi, proj)
+    for seg in (1, 4, -1):
+        tuning("fom_segment_steps", seg)
+        U, it = fem.pod_prom_burgers_batch(0.05, nT, np.ones(512), mu1, 0.0, mu2, Phi, proj)
+        assert torch.equal(it, it0), seg
+        rel = (torch.linalg.norm(U - U0, dim=2) / torch.linalg.norm(U0, dim=2)).max().item()
+        assert rel <= 1e-12, (seg, rel)
+    sel = np.arange(0, B, 211)
+    Us = U.cpu().numpy()[sel]; its = it.cpu().numpy()[sel]
+    for j, b in enumerate(sel):
+        Uo, ito = oracle.pod_prom_burgers(X, 0.05, nT, np.ones(512), mu1[b], 0.0, mu2[b], Phi, proj)
+        assert np.array_equal(its[j], ito), b
+        assert np.max(np.linalg.norm(Us[j].T - Uo, axis=0) / np.linalg.norm(Uo, axis=0)) <= 1e-10, b
+
+
+@pytest.mark.parametrize("n", [21, 28])
+def test_qm_segmented_sweep_is_bit_identical(n, oracle, tuning):
+    """Quadratic-manifold kernel (csrc/bx_qm.cu, both tangent-row schedules by n) with more lock-step groups than SMs:
+    every step starts from q = Phi^T U^m of the stored snapshot (:1129), so a resumed group reproduces the running one
+    bit for bit."""
+    import burgers_b200
+    from conftest import GOLDEN
+    X, _ = oracle.mesh(512)
+    fem = burgers_b200.FEMBurgers(X)
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    B = 8 * sms + 77
+    rng = np.random.default_rng(9)
+    mu1 = 4.25 + 1.25 * rng.random(B); mu2 = 0.015 + 0.015 * rng.random(B)
+    if n == 21:
+        Phi = np.load(f"{GOLDEN}/qm_Phi.npy"); H = np.load(f"{GOLDEN}/qm_H.npy")
+    else:
+        m1, m2 = oracle.parameter_grid(3, 3)
+        Ut, _ = fem.fom_burgers_batch(0.05, 500, np.ones(512), m1, 0.0, m2)
+        S = np.ascontiguousarray(Ut.cpu().numpy().reshape(-1, 512).T)
+        Phi = _phi(n); q = Phi.T @ S
+        H = np.ascontiguousarray(oracle.compute_H(oracle.build_Q(q), oracle.build_E(S, Phi, q), 1e-2))
+    nT = 7
+    tuning("fom_segment_steps", 0)
+    U0, it0 = fem.pod_quadratic_manifold_batch(0.05, nT, np.ones(512), mu1, 0.0, mu2, Phi, H, "LSPG")
+    for seg in (1, 3, -1):
+        tuning("fom_segment_steps", seg)
+        U, it = fem.pod_quadratic_manifold_batch(0.05, nT, np.ones(512), mu1, 0.0, mu2, Phi, H, "LSPG")
+        assert torch.equal(it, it0), seg
+        assert torch.equal(U, U0), seg
+    b = B - 3
+    Uo, ito = oracle.pod_quadratic_manifold(X, 0.05, nT, np.ones(512), mu1[b], 0.0, mu2[b], Phi, H, "LSPG")
+    assert np.array_equal(it0[b].cpu().numpy(), ito)
+    assert np.max(np.linalg.norm(U0[b].cpu().numpy().T - Uo, axis=0) / np.linalg.norm(Uo, axis=0)) <= 1e-10
