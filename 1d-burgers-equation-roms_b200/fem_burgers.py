@@ -466,5 +466,128 @@ class FEMBurgers:
         self._check_finite("pod_quadratic_manifold", singular=True)
         return U
 
+    # -- reduced system for a caller-supplied tangent and its first consumer, local POD ------------
+    @_on_device
+    def reduced_system_batch(self, At, E, Uk, Un, mu1, mu2, T, projection="Galerkin", supg=True, out=None):
+        """Ar, br of ONE nonlinear iteration (FEM/fem_burgers.py:730-762 and the same block in local_prom_burgers,
+        pod_ann_prom, pod_rbf_prom, lie_prom, ae_prom) for B samples: Uk, Un (B, N); mu1, mu2 (B,); T the decoder
+        tangent, (N, n) shared by all samples or (B, N, n) one per sample.  Returns CUDA tensors Ar (B, n, n),
+        br (B, n); the caller solves and updates with its own decoder (np.linalg.solve(Ar, -br) at :767)."""
+        code = self._projection_code(projection)
+        Uk = self._dev(Uk); Un = self._dev(Un)
+        N = self.n_nodes
+        if Uk.dim() == 1:
+            Uk = Uk.reshape(1, N)
+        if Un.dim() == 1:
+            Un = Un.reshape(1, N)
+        B = Uk.shape[0]
+        if tuple(Uk.shape) != (B, N) or tuple(Un.shape) != (B, N):
+            raise ValueError("Uk and Un must have shape (B, N)")
+        mu1 = self._dev(np.atleast_1d(mu1) if not isinstance(mu1, torch.Tensor) else mu1).reshape(-1)
+        mu2 = self._dev(np.atleast_1d(mu2) if not isinstance(mu2, torch.Tensor) else mu2).reshape(-1)
+        if mu1.numel() != B or mu2.numel() != B:
+            raise ValueError("mu1 and mu2 must have one entry per sample")
+        T = self._dev(T)
+        if T.dim() == 2 and T.shape[0] == N:
+            n, stride = int(T.shape[1]), 0
+        elif T.dim() == 3 and tuple(T.shape[:2]) == (B, N):
+            n, stride = int(T.shape[2]), N * int(T.shape[2])
+        else:
+            raise ValueError("T must have shape (N, n) or (B, N, n)")
+        if out is None:
+            Ar = self._new(B, n, n); br = self._new(B, n)
+        else:
+            Ar, br = out
+            if tuple(Ar.shape) != (B, n, n) or tuple(br.shape) != (B, n) or Ar.dtype != torch.float64 \
+                    or br.dtype != torch.float64 or not Ar.is_contiguous() or not br.is_contiguous() \
+                    or Ar.device != self.device or br.device != self.device:
+                raise ValueError(f"out must be contiguous float64 tensors (B, n, n) and (B, n) on {self.device}")
+        if B == 0:
+            return Ar, br
+        lib = _lib.load()
+        _lib.check(lib.bx_reduced_system(B, N, n, _ptr(self.Xd), _ptr(Uk), _ptr(Un), _ptr(mu1), _ptr(mu2), float(At),
+                                         float(E), 1 if supg else 0, _ptr(T), stride, code, _ptr(Ar), _ptr(br),
+                                         self._stream()), "bx_reduced_system")
+        return Ar, br
+
+    @_on_device
+    def local_prom_burgers_batch(self, At, nTimeSteps, u0, mu1, E, mu2, cluster_centers, local_bases, U_global,
+                                 num_global_modes, projection="Galerkin", tol=1e-6, kmax=20):
+        """local_prom_burgers (FEM/fem_burgers.py:979-1078) for B samples in lock step.  cluster_centers: (K, g) k-means
+        centres (`kmeans.cluster_centers_`; `kmeans.predict` = nearest centre, :1011); local_bases: dict or sequence
+        of K arrays (N, n_c); U_global: (N, >= g).  Every time step picks ONE basis per sample from the cluster of
+        U_global[:, :g]^T U^n (:1010-1012); every Picard iteration is one bx_reduced_system call with a per-sample
+        tangent, one batched solve (cuSOLVER) and two batched products for q = Phi^T U0 + dq, U1 = Phi q (:1061-1067).
+        Bases are padded with zero columns to the widest one (their rows / columns of Ar become the identity).
+        Returns U (B, nTimeSteps+1, N), iters (B, nTimeSteps) int32, clusters (B, nTimeSteps) int64: CUDA tensors."""
+        self._projection_code(projection)
+        N = self.n_nodes
+        mu1 = self._dev(np.atleast_1d(mu1) if not isinstance(mu1, torch.Tensor) else mu1).reshape(-1)
+        mu2 = self._dev(np.atleast_1d(mu2) if not isinstance(mu2, torch.Tensor) else mu2).reshape(-1)
+        B = mu1.numel()
+        if mu2.numel() != B:
+            raise ValueError("mu1 and mu2 must have the same number of samples")
+        nT = int(nTimeSteps)
+        g = int(num_global_modes)
+        centers = self._dev(cluster_centers)
+        K = centers.shape[0]
+        bases = [local_bases[c] for c in range(K)] if isinstance(local_bases, dict) else list(local_bases)
+        if len(bases) != K:
+            raise ValueError("one local basis per cluster centre is required")
+        widths = [int(np.shape(b)[1]) for b in bases]
+        nmax = max(widths)
+        Phi_all = torch.zeros((K, N, nmax), dtype=torch.float64, device=self.device)
+        for c, b in enumerate(bases):
+            Phi_all[c, :, :widths[c]] = self._dev(b)
+        pad = torch.zeros((K, nmax), dtype=torch.float64, device=self.device)
+        for c in range(K):
+            pad[c, widths[c]:] = 1.0
+        Ug = self._dev(U_global)[:, :g].contiguous()
+        if centers.shape[1] != g:
+            raise ValueError("cluster centres and num_global_modes disagree")
+        U = self._new(B, nT + 1, N)
+        iters = self._new(B, nT, dtype=torch.int32)
+        clusters = torch.empty((B, nT), dtype=torch.int64, device=self.device)
+        u0 = self._dev(u0)
+        U[:, 0] = u0 if u0.numel() == B * N else u0.reshape(1, N)
+        Ar = self._new(B, nmax, nmax); br = self._new(B, nmax)
+        for n in range(nT):
+            Un = U[:, n].contiguous()
+            qg = Un @ Ug                                                     # (B, g)
+            cid = torch.cdist(qg, centers).argmin(dim=1)                     # nearest centre (:1011)
+            clusters[:, n] = cid
+            T = Phi_all[cid].contiguous()                                    # (B, N, nmax)
+            eye_pad = torch.diag_embed(pad[cid])
+            U0 = Un.clone()
+            active = torch.ones(B, dtype=torch.bool, device=self.device)
+            count = torch.zeros(B, dtype=torch.int32, device=self.device)
+            for k in range(int(kmax)):
+                self.reduced_system_batch(At, E, U0, Un, mu1, mu2, T, projection, supg=True, out=(Ar, br))
+                dq = torch.linalg.solve(Ar + eye_pad, -br.unsqueeze(2)).squeeze(2)          # :1058
+                q = torch.bmm(T.transpose(1, 2), U0.unsqueeze(2)).squeeze(2) + dq           # :1061
+                U1 = torch.bmm(T, q.unsqueeze(2)).squeeze(2)                                # :1064
+                err = torch.linalg.norm(dq, dim=1) / torch.linalg.norm(q, dim=1)            # :1067
+                U0 = torch.where(active.unsqueeze(1), U1, U0)
+                count += active.to(torch.int32)
+                active = active & (err > tol)
+                if not bool(active.any()):
+                    break
+            U[:, n + 1] = U0
+            iters[:, n] = count
+        return U, iters, clusters
+
+    def local_prom_burgers(self, At, nTimeSteps, u0, mu1, E, mu2, kmeans, local_bases, U_global, num_global_modes,
+                           projection="Galerkin"):
+        """Drop-in for FEMBurgers.local_prom_burgers (:979-1078): `kmeans` is the fitted sklearn model the reference
+        passes (only its cluster_centers_ are read; predict = nearest centre), or the (K, g) array of centres.
+        Returns ndarray (N, nTimeSteps+1); per-step iteration counts in self.last_iters, clusters in self.last_clusters."""
+        centers = getattr(kmeans, "cluster_centers_", kmeans)
+        U, it, cl = self.local_prom_burgers_batch(At, nTimeSteps, np.asarray(u0, dtype=np.float64), [float(mu1)], E,
+                                                  [float(mu2)], np.asarray(centers, dtype=np.float64), local_bases,
+                                                  np.asarray(U_global, dtype=np.float64), num_global_modes, projection)
+        self.last_iters = it[0].cpu().numpy()
+        self.last_clusters = cl[0].cpu().numpy()
+        return np.ascontiguousarray(U[0].cpu().numpy().T)
+
     # the north_star's name for the same method
     pod_prom_newton = pod_prom_burgers

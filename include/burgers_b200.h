@@ -159,6 +159,19 @@ int bx_prom_trajectories(int B, int N, int n, int nsteps, const double *X, const
                          const double *Phi, int projection, double tol, int kmax,
                          double *U, int *iters, double *err_hist, void *workspace, void *stream);
 
+/* The reduced system of ONE nonlinear iteration for a caller-supplied tangent: the block every
+ * PROM variant of the reference repeats with its own decoder tangent in the place of Phi — pod_prom_burgers
+ * FEM/fem_burgers.py:730-762, local_prom_burgers :1022-1058, pod_ann_prom :1225-1262, pod_rbf_prom :1330-1375,
+ * lie_prom, ae_prom.  Native precedent with the same in-place-output shape: compute_Ar_br(A, Phi, R, Ar, br,
+ * echo_level), Stanford_2D/Burgers_2D/cpp_files/mkl_sparse_dense_operations.cpp:13-20.
+ *   A = M + At C(Uk) + At E K (row 0 <- e0^T);  b = M Un + At F(mu2) - At S(Uk, mu2) [supg != 0], b[0] = mu1;
+ *   R = A Uk - b;   Galerkin: Ar = T^T A T, br = T^T R;   LSPG: Ar = (A T)^T (A T), br = (A T)^T R.
+ * Uk, Un: (B, N).  T: (N, n) row-major, shared by all samples (T_stride = 0) or one per sample, T_stride doubles
+ * apart (>= N n).  Ar: (B, n, n) row-major, br: (B, n).  n <= 240, N <= 2048.  No workspace.               */
+int bx_reduced_system(int B, int N, int n, const double *X, const double *Uk, const double *Un,
+                      const double *mu1, const double *mu2, double At, double E, int supg,
+                      const double *T, long long T_stride, int projection, double *Ar, double *br, void *stream);
+
 /* FEMBurgers.pod_quadratic_manifold, FEM/fem_burgers.py:1081-1175, for B samples at once.
  * Decoder u = Phi q + H sym(q x q), tangent Phi + H dQ/dq (get_single_Q / get_dQ_dq, :275-312; monomial
  * order i outer, j >= i inner).  Phi: (N, n), H: (N, n(n+1)/2), both row-major, shared by all samples.
