@@ -1,4 +1,4 @@
-"""Time the quadratic-manifold PROM sweep on cuda:0: python tools/qm_time.py [B] [proj] [steps] [n]
+"""Time the quadratic-manifold PROM sweep on cuda:0: python tools/qm_time.py [B] [proj] [steps] [n] [schedule]
 n = 21 uses the reference's stored Phi/H; other n truncate Phi and ridge-fit H from FOM snapshots."""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -10,6 +10,8 @@ B = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
 proj = sys.argv[2] if len(sys.argv) > 2 else "Galerkin"
 steps = int(sys.argv[3]) if len(sys.argv) > 3 else 500
 n = int(sys.argv[4]) if len(sys.argv) > 4 else 21
+if len(sys.argv) > 5:
+    burgers_b200.set_tuning("qm_schedule", int(sys.argv[5]))   # 0 v2 / 1 shared tile / 2 chunked global
 G = os.path.join(os.path.dirname(__file__), "..", "tests", "golden")
 X = np.linspace(0, 100, 512)
 fem = burgers_b200.FEMBurgers(X)
