@@ -32,25 +32,6 @@
 
 namespace bx {
 
-struct PromParams {
-    int B, N, n, nsteps, kmax, ldp, warps;
-    const double *X;
-    const double *u0;
-    long long u0_stride;
-    const double *mu1;
-    const double *mu2;
-    double At, E, tol;
-    const double *Phi;   // (N, n) row-major (C order), shared by all samples
-    double *atf;         // workspace: At * F            (B, N)
-    double *hfs;         // workspace: (h/6)(f_gp1+f_gp2) (B, N), element e at [e]
-    double *U;
-    int *iters;
-    double *err_hist;    // optional (B, nsteps, kmax): |dq| / |q| after every iteration (:776)
-    unsigned int *counter;
-    int *progress;       // workspace: (B,) segments completed per trajectory (-1: not finite any more); nseg > 1 only
-    int nseg, seg;       // the nsteps time steps are cut into nseg segments of seg steps, handed out round-robin
-};
-
 constexpr int PROM_MAXW = 8;
 
 // shared-memory carve-up, in doubles.  Node/element arrays are skewed by one word per run so
@@ -111,6 +92,9 @@ int launch_prom_forcing(int B, int N, const double *X, const double *mu2, double
     BX_LAUNCH_CHECK();
     return BX_OK;
 }
+
+// bx_prom_wide.cu: one warp per trajectory, 32 <= n <= 47 (register accumulators, reduced solve in shared memory)
+int launch_prom_wide(const PromParams &p, bool lspg, cudaStream_t st);
 
 // bx_prom_cta.cu: one CTA per trajectory, 32 <= n <= 240
 int launch_prom_cta(int B, int N, int n, int nsteps, const double *X, const double *u0, int u0_batched,
@@ -538,7 +522,9 @@ extern "C" int bx_prom_trajectories(int B, int N, int n, int nsteps, const doubl
     BX_REQUIRE(kmax >= 1, "kmax must be >= 1 (the reference loop body defines U1)");
     if (B == 0) return BX_OK;
     BX_REQUIRE(X && u0 && mu1 && mu2 && Phi && U && workspace, "null device pointer");
-    if (n >= 32) {
+    // 32 <= n <= 48: the register kernel (bx_prom_wide.cu); BX_TUNE_PROM_WARPS_PER_TRAJECTORY = 8 forces the CTA kernel
+    const bool wide = n >= 32 && n <= 48 && tuning(BX_TUNE_PROM_WARPS_PER_TRAJECTORY) != 8;
+    if (n >= 32 && !wide) {
         if (n > 240) {
             set_error("bx_prom_trajectories: n = %d modes > 240 is not supported by this build", n);
             return BX_ERR_UNSUPPORTED;
@@ -559,5 +545,6 @@ extern "C" int bx_prom_trajectories(int B, int N, int n, int nsteps, const doubl
     p.progress = reinterpret_cast<int *>(p.hfs + (size_t)B * N);
     p.nseg = 1; p.seg = nsteps > 0 ? nsteps : 1;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (wide) return launch_prom_wide(p, projection == BX_LSPG, st);
     return projection == BX_LSPG ? launch_prom<true>(p, st) : launch_prom<false>(p, st);
 }

@@ -6,6 +6,26 @@
 
 namespace bx {
 
+// parameter block of the warp-per-trajectory POD-PROM kernels (bx_prom.cu: n <= 31, bx_prom_wide.cu: 32 <= n <= 47)
+struct PromParams {
+    int B, N, n, nsteps, kmax, ldp, warps;
+    const double *X;
+    const double *u0;
+    long long u0_stride;
+    const double *mu1;
+    const double *mu2;
+    double At, E, tol;
+    const double *Phi;   // (N, n) row-major (C order), shared by all samples
+    double *atf;         // workspace: At * F            (B, N)
+    double *hfs;         // workspace: (h/6)(f_gp1+f_gp2) (B, N), element e at [e]
+    double *U;
+    int *iters;
+    double *err_hist;    // optional (B, nsteps, kmax): |dq| / |q| after every iteration (:776)
+    unsigned int *counter;
+    int *progress;       // workspace: (B,) segments completed per trajectory (-1: not finite any more); nseg > 1 only
+    int nseg, seg;       // the nsteps time steps are cut into nseg segments of seg steps, handed out round-robin
+};
+
 constexpr int MAT_LD = 33;   // row stride of the dense reduced system (odd: conflict-free row reads)
 
 __device__ __forceinline__ void dmma884(double &c0, double &c1, double a, double b) {

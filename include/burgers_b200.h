@@ -60,7 +60,7 @@ int         bx_device_sm_count(void);
 #define BX_TUNE_PROM_CTA_CHUNK           2  /* 8, 12, 16, 24 or 32 nodes per staged Phi chunk, n >= 32   */
 #define BX_TUNE_QM_SCHEDULE              3  /* tangent rows of the quadratic-manifold PROM:
                                                0 global scratch, 1 shared-memory tile, 2 chunked global   */
-#define BX_TUNE_PROM_WARPS_PER_TRAJECTORY 4 /* 1 or 2 warps integrate one POD-PROM trajectory (n <= 31)   */
+#define BX_TUNE_PROM_WARPS_PER_TRAJECTORY 4 /* POD PROM with 32 <= n <= 48: 1 = one warp per trajectory (default), 8 = the CTA kernel */
 #define BX_TUNE_FOM_KERNEL               5  /* 0 throughput kernel, 1 latency kernel (speculative front half) */
 #define BX_TUNE_FOM_SEGMENT_STEPS        6  /* time steps per round-robin work unit of the FOM / POD-PROM / quadratic-manifold sweeps (0: whole trajectories) */
 #define BX_TUNE_QM_GROUP                 7  /* 1 .. 8 trajectories per lock-step group of the quadratic-manifold PROM */

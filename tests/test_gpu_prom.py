@@ -115,6 +115,35 @@ def test_large_basis_vs_oracle(N, n, proj, oracle):
         assert rel_l2_per_step(U[b].T, Uo) <= TOL, b
 
 
+@pytest.mark.parametrize("kernel", ["register", "cta"])
+@pytest.mark.parametrize("N,n", [(512, 32), (512, 33), (512, 39), (512, 40), (512, 41), (300, 47), (512, 48), (64, 40), (1000, 40)])
+@pytest.mark.parametrize("proj", ["LSPG", "Galerkin"])
+def test_32_to_48_modes_both_kernels_vs_oracle(N, n, proj, kernel, oracle):
+    """32 <= n <= 48: the one-warp-per-trajectory register kernel (csrc/bx_prom_wide.cu; NB = 5 / 6 column blocks, R beside
+    the tiles at n = 40 and 48, reduced solve in shared memory with dgetf2's pivot order) and the CTA kernel forced through
+    the tuning knob, more samples than one CTA holds, a batched u0."""
+    import burgers_b200
+    if n > N:
+        pytest.skip("n <= N")
+    X = np.linspace(0.0, 100.0 * (N - 1) / 511.0, N)
+    fem = burgers_b200.FEMBurgers(X)
+    Phi = _big_basis(oracle, X, n)
+    rng = np.random.default_rng(n)
+    B = 11
+    mu1 = 4.3 + 1.1 * rng.random(B); mu2 = 0.016 + 0.013 * rng.random(B)
+    u0 = 1.0 + 0.02 * rng.random((B, N))
+    burgers_b200.set_tuning("prom_warps_per_trajectory", 8 if kernel == "cta" else -1)
+    try:
+        U, it = fem.pod_prom_burgers_batch(0.05, 4, u0, mu1, 0.0, mu2, Phi, proj)
+    finally:
+        burgers_b200.set_tuning("prom_warps_per_trajectory", -1)
+    U = U.cpu().numpy(); it = it.cpu().numpy()
+    for b in (0, 5, 10):
+        Uo, ito = oracle.pod_prom_burgers(X, 0.05, 4, u0[b], mu1[b], 0.0, mu2[b], Phi, proj)
+        assert np.array_equal(it[b], ito), (b, it[b], ito)
+        assert rel_l2_per_step(U[b].T, Uo) <= TOL, b
+
+
 def test_too_many_modes_is_an_error(oracle, fem512):
     import burgers_b200
     X, _ = oracle.mesh(512)

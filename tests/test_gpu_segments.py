@@ -77,9 +77,10 @@ def _phi(n):
     return np.ascontiguousarray(np.load(f"{GOLDEN}/Phi_tol_1e-04.npy")[:, :n])
 
 
+@pytest.mark.parametrize("nmodes", [28, 40])
 @pytest.mark.parametrize("proj", ["LSPG", "Galerkin"])
-def test_prom_segmented_sweep_matches_whole_trajectories(proj, oracle, tuning):
-    """POD-PROM warp kernel (csrc/bx_prom.cu) with more trajectories than warp slots: round-robin segments against whole
+def test_prom_segmented_sweep_matches_whole_trajectories(proj, nmodes, oracle, tuning):
+    """POD-PROM warp kernels (csrc/bx_prom.cu at 28 modes, csrc/bx_prom_wide.cu at 40) with more trajectories than warp slots: round-robin segments against whole
     trajectories from the queue.  A resumed trajectory projects its snapshot explicitly (q0 = Phi^T U, as the reference
     does at :770) where the running one uses (Phi^T Phi) q, so the two agree to rounding, not bit for bit: 1e-12 per
     step and identical counts; both against the oracle on a strided sample."""
@@ -90,7 +91,7 @@ def test_prom_segmented_sweep_matches_whole_trajectories(proj, oracle, tuning):
     B = 8 * sms + 150
     rng = np.random.default_rng(7)
     mu1 = 4.25 + 1.25 * rng.random(B); mu2 = 0.015 + 0.015 * rng.random(B)
-    Phi = _phi(28)
+    Phi = _phi(nmodes)
     nT = 11
     tuning("fom_segment_steps", 0)
     U0, it0 = fem.pod_prom_burgers_batch(0.05, nT, np.ones(512), mu1, 0.0, mu2, Phi, proj)
