@@ -18,10 +18,21 @@
 //   * every per-mode vector (q, dq, q0) has two entries per lane (modes lane and lane + 32).
 // Work units are segments of trajectories handed out round-robin, as in bx_prom.cu / bx_fom.cu.
 #include "bx_prom_common.cuh"
+#include <utility>
 
 namespace bx {
 
 constexpr int PW_MAXW = 8;
+
+// compile-time loop: f(integral_constant<int, 0>) ... f(integral_constant<int, N - 1>), in order (the elimination
+// steps index register arrays, so the step number has to be a constant: `#pragma unroll` gives up on loops this size)
+template <class F, int... Is>
+__device__ __forceinline__ void static_for_impl(F &&f, std::integer_sequence<int, Is...>) {
+    (f(std::integral_constant<int, Is>{}), ...);
+}
+template <int N, class F> __device__ __forceinline__ void static_for(F &&f) {
+    static_for_impl(static_cast<F &&>(f), std::make_integer_sequence<int, N>{});
+}
 
 struct PromWideSmem {
     int h6, gm, per_cta;
@@ -47,8 +58,86 @@ struct PromWideSmem {
     }
 };
 
-// Solve the n x n system held in shared memory (rows r < n at M + r * ldm, right-hand side in column NC of each row)
-// by one warp; lanes own rows `lane` and `lane + 32`.  Returns with the solution in column NC.
+// n x n solve, 32 < n <= 64, TWO matrix rows per lane (rows `lane` and `lane + 32`), columns in registers: the
+// two-row version of lu_solve_rows (bx_prom_common.cuh).  a0 / a1: the lane's rows of Ar (a1 all zero when
+// lane + 32 >= n), rhs0 / rhs1 = -br.  PIVOT: partial pivoting in the elimination order of LAPACK dgetf2 (maximal
+// |a_ik| among the remaining rows, scaling by the reciprocal pivot; np.linalg.solve -> gesv, :767), rows never move
+// (implicit pivoting).  !PIVOT: natural order (the SPD LSPG normal matrix).  The pivot row of step k goes through a
+// double-buffered shared-memory row (pb: 2 x (NC + 2) doubles, 16-byte aligned).  Returns x[lane], x[lane + 32].
+template <int NC, bool PIVOT>
+__device__ __forceinline__ void lu_solve_rows2(double (&a0)[NC], double (&a1)[NC], double rhs0, double rhs1, int n,
+                                               int lane, double *pb, double &x0, double &x1) {
+    constexpr int PLD = NC + 2;
+    bool av0 = lane < n, av1 = lane + 32 < n;   // row not yet used as a pivot row
+    int ms0 = -1, ms1 = -1;                     // elimination step at which the row became the pivot row
+    double pinv0 = 0.0, pinv1 = 0.0;
+    int prs[NC];                                // pivot row of every step (warp-uniform)
+    static_for<NC>([&](auto kc) {
+        constexpr int k = decltype(kc)::value;
+        prs[k] = k;
+        if (k < n) {
+            int pr = k;
+            if (PIVOT) {
+                const double v0 = av0 ? fabs(a0[k]) : -1.0, v1 = av1 ? fabs(a1[k]) : -1.0;
+                const bool take1 = v1 > v0;
+                const double v = take1 ? v1 : v0;
+                const unsigned long long key = v >= 0.0 ? (unsigned long long)__double_as_longlong(v) + 1ull : 0ull;
+                const unsigned khi = (unsigned)(key >> 32), klo = (unsigned)key;
+                const unsigned mhi = __reduce_max_sync(FULL, khi);
+                const bool c1 = khi == mhi;
+                const unsigned mlo = __reduce_max_sync(FULL, c1 ? klo : 0u);
+                const unsigned cand = (c1 && klo == mlo && key != 0ull) ? (unsigned)(lane + (take1 ? 32 : 0)) : 0xffffu;
+                const unsigned best = __reduce_min_sync(FULL, cand);
+                pr = best == 0xffffu ? k : (int)best;
+                prs[k] = pr;
+            }
+            const int pl = pr & 31;
+            const bool ps = pr >= 32;
+            const int kk = k & ~1;
+            double2 *row2 = reinterpret_cast<double2 *>(pb + (k & 1) * PLD);
+            if (lane == pl) {
+#pragma unroll
+                for (int j = kk; j < NC; j += 2)
+                    row2[j >> 1] = ps ? make_double2(a1[j], a1[j + 1]) : make_double2(a0[j], a0[j + 1]);
+                pb[(k & 1) * PLD + NC] = ps ? rhs1 : rhs0;
+            }
+            __syncwarp();
+            double prow[NC];
+#pragma unroll
+            for (int j = kk; j < NC; j += 2) {
+                const double2 v = row2[j >> 1];
+                prow[j] = v.x; prow[j + 1] = v.y;
+            }
+            const double prhs = pb[(k & 1) * PLD + NC];
+            const double inv = rcp(prow[k]);
+            const bool self0 = lane == pl && !ps, self1 = lane == pl && ps;
+            const double l0 = (av0 && !self0) ? a0[k] * inv : 0.0;
+            const double l1 = (av1 && !self1) ? a1[k] * inv : 0.0;
+#pragma unroll
+            for (int j = k + 1; j < NC; ++j) { a0[j] = fma(-l0, prow[j], a0[j]); a1[j] = fma(-l1, prow[j], a1[j]); }
+            rhs0 = fma(-l0, prhs, rhs0);
+            rhs1 = fma(-l1, prhs, rhs1);
+            if (self0) { av0 = false; ms0 = k; pinv0 = inv; }
+            if (self1) { av1 = false; ms1 = k; pinv1 = inv; }
+        }
+    });
+    x0 = 0.0; x1 = 0.0;
+    static_for<NC>([&](auto kc) {
+        constexpr int k = NC - 1 - decltype(kc)::value;
+        if (k < n) {
+            const int pr = prs[k];
+            const double mine = pr >= 32 ? rhs1 * pinv1 : rhs0 * pinv0;
+            const double xk = shfl_idx(mine, pr & 31);
+            if (ms0 < k) rhs0 = fma(-a0[k], xk, rhs0);
+            if (ms1 < k) rhs1 = fma(-a1[k], xk, rhs1);
+            if (lane == (k & 31)) { if (k >= 32) x1 = xk; else x0 = xk; }
+        }
+    });
+}
+
+// Variant: the same solve out of shared memory (rows r < n at M + r * ldm, right-hand side in column NC), lanes own rows
+// `lane` and `lane + 32`; physical row swaps in dgetf2's order.  Cost grows with n^3 (the register version always pays
+// for NC columns) and it needs no registers beside the contraction's.  Returns with the solution in column NC.
 template <int NC, bool PIVOT>
 __device__ __forceinline__ void lu_solve_smem(double *M, int ldm, int n, int lane) {
     const int r0 = lane, r1 = lane + 32;
@@ -90,8 +179,7 @@ __device__ __forceinline__ void lu_solve_smem(double *M, int ldm, int n, int lan
         }
         __syncwarp();
     }
-    // back substitution, column oriented: x[k] = rhs[k] / u_kk, then rhs[r] -= u_rk x[k] for r < k
-    for (int k = n - 1; k >= 0; --k) {
+    for (int k = n - 1; k >= 0; --k) {   // back substitution, column oriented
         const double xk = M[k * ldm + NC] * rcp(M[k * ldm + k]);
         __syncwarp();
         if (lane == 0) M[k * ldm + NC] = xk;
@@ -101,8 +189,12 @@ __device__ __forceinline__ void lu_solve_smem(double *M, int ldm, int n, int lan
     }
 }
 
-// RSEP: n == 8 NB, R does not ride as a column of the right operand (br accumulated beside the tiles)
-template <int NB, bool LSPG, bool RSEP>
+// RSEP: n == 8 NB, R does not ride as a column of the right operand (br accumulated beside the tiles).
+// SLU: reduced solve out of shared memory (lu_solve_smem) instead of registers (lu_solve_rows2).  Measured at 4096
+// samples (profiles/r2u_prom_wide_variants.txt): the pivoted solve is faster out of shared memory at every n (n = 40
+// Galerkin 7.7 against 6.0 M it/s), the unpivoted LSPG solve is faster in registers from n = 36 on (n = 40: 11.1 against
+// 9.2 M it/s; n = 32: 12.0 against 13.2).  A deeper prefetch of the Phi rows (three k-steps ahead) changed nothing.
+template <int NB, bool LSPG, bool RSEP, bool SLU>
 __global__ void __launch_bounds__(PW_MAXW * 32, 1) prom_wide_kernel(const PromParams p) {
     constexpr int NC = NB * 8;
     using Tl = PromTiles<NB, LSPG>;
@@ -224,32 +316,26 @@ __global__ void __launch_bounds__(PW_MAXW * 32, 1) prom_wide_kernel(const PromPa
                 double brp[NB];
 #pragma unroll
                 for (int b = 0; b < NB; ++b) brp[b] = 0.0;
+                // Phi rows of the nodes run0 + s - 1, s, s + 1 (rolling three-row window; the rows come from L1 / L2)
                 double pm[NB], p0[NB], pp[NB];
-                {
-                    const double *rm = p.Phi + (size_t)(run0 > 0 ? run0 - 1 : 0) * n;
-                    const double *r0p = p.Phi + (size_t)(run0 < N ? run0 : 0) * n;
-                    const bool okm = t > 0 && run0 - 1 < N;
-                    const bool ok0 = run0 < N;
+                auto phi_row = [&](double (&dst)[NB], int inx) {
+                    const bool ok = inx >= 0 && inx < N;
+                    const double *rp = p.Phi + (size_t)(ok ? inx : 0) * n;
 #pragma unroll
                     for (int b = 0; b < NB; ++b) {
                         const bool cok = (b < NB - 1) || col_last;
-                        pm[b] = (cok && okm) ? rm[b * 8 + g] : 0.0;
-                        p0[b] = (cok && ok0) ? r0p[b * 8 + g] : 0.0;
+                        dst[b] = (cok && ok) ? rp[b * 8 + g] : 0.0;
                     }
-                }
+                };
+                phi_row(pm, t > 0 ? run0 - 1 : -1);
+                phi_row(p0, run0);
                 PromRow nxt = prom_row(rc, run0 + g, ubase + g);
                 for (int blk = 0; blk < nblk; ++blk) {
                     const PromRow cur = nxt;
                     if (blk + 1 < nblk) nxt = prom_row(rc, run0 + ((blk + 1) << 3) + g, ubase + ((blk + 1) << 3) + g);
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
-                        const int inx = run0 + (blk << 3) + j + 1;
-                        const double *rp = p.Phi + (size_t)(inx < N ? inx : 0) * n;
-#pragma unroll
-                        for (int b = 0; b < NB; ++b) {
-                            const bool cok = (b < NB - 1) || col_last;
-                            pp[b] = (cok && inx < N) ? rp[b * 8 + g] : 0.0;
-                        }
+                        phi_row(pp, run0 + (blk << 3) + j + 1);
                         const int src = 4 * j + t;
                         const double ra = shfl_idx(cur.a, src), rb = shfl_idx(cur.b, src);
                         const double rcc = shfl_idx(cur.c, src), rR = shfl_idx(cur.R, src);
@@ -304,9 +390,21 @@ __global__ void __launch_bounds__(PW_MAXW * 32, 1) prom_wide_kernel(const PromPa
                     if (has1) w_mat[m1 * ldm + NC] = -w_mat[m1 * ldm + n];
                     __syncwarp();
                 }
-                lu_solve_smem<NC, !LSPG>(w_mat, ldm, n, lane);
-                const double dq0 = m0 < n ? w_mat[m0 * ldm + NC] : 0.0;
-                const double dq1 = has1 ? w_mat[m1 * ldm + NC] : 0.0;
+                double dq0, dq1;
+                if constexpr (SLU) {
+                    lu_solve_smem<NC, !LSPG>(w_mat, ldm, n, lane);
+                    dq0 = w_mat[m0 * ldm + NC];
+                    dq1 = has1 ? w_mat[m1 * ldm + NC] : 0.0;
+                } else {
+                    double a0[NC], a1[NC];
+                    const double *mr0 = w_mat + m0 * ldm, *mr1 = w_mat + (has1 ? m1 : m0) * ldm;
+#pragma unroll
+                    for (int j = 0; j < NC; ++j) { a0[j] = mr0[j]; a1[j] = has1 ? mr1[j] : 0.0; }
+                    const double rhs0 = mr0[NC], rhs1 = has1 ? mr1[NC] : 0.0;
+                    __syncwarp();   // every row is in registers: the matrix area now carries the pivot rows
+                    lu_solve_rows2<NC, !LSPG>(a0, a1, rhs0, rhs1, n, lane, w_mat, dq0, dq1);
+                    if (!has1) dq1 = 0.0;
+                }
                 const double qa = m0 < n ? q00 + dq0 : 0.0;   // q = Phi^T U_k + dq (:770)
                 const double qb = has1 ? q01 + dq1 : 0.0;
                 const double sd = warp_sum(fma(dq0, dq0, dq1 * dq1));
@@ -392,7 +490,7 @@ __global__ void __launch_bounds__(PW_MAXW * 32, 1) prom_wide_kernel(const PromPa
 int launch_prom_forcing(int B, int N, const double *X, const double *mu2, double At, double *atf, double *hfs,
                         cudaStream_t st);
 
-template <int NB, bool LSPG, bool RSEP>
+template <int NB, bool LSPG, bool RSEP, bool SLU>
 static int launch_wide_t(PromParams p, cudaStream_t st) {
     const PromGeom geo = PromGeom::make(p.N);
     const PromWideSmem lay = PromWideSmem::make(geo.NP, NB * 8);
@@ -414,7 +512,7 @@ static int launch_wide_t(PromParams p, cudaStream_t st) {
     }
     p.warps = (int)warps;
     const size_t smem = sizeof(double) * ((size_t)lay.per_cta + (size_t)warps * lay.per_warp);
-    auto kern = prom_wide_kernel<NB, LSPG, RSEP>;
+    auto kern = prom_wide_kernel<NB, LSPG, RSEP, SLU>;
     {
         const int rco = kernel_occupancy(reinterpret_cast<const void *>(kern), (int)warps * 32, smem, nullptr);
         if (rco != BX_OK) return rco;
@@ -441,10 +539,14 @@ static int launch_wide_t(PromParams p, cudaStream_t st) {
 
 template <bool LSPG>
 static int launch_wide(const PromParams &p, cudaStream_t st) {
-    if (p.n == 40) return launch_wide_t<5, LSPG, true>(p, st);
-    if (p.n < 40) return launch_wide_t<5, LSPG, false>(p, st);
-    if (p.n == 48) return launch_wide_t<6, LSPG, true>(p, st);
-    return launch_wide_t<6, LSPG, false>(p, st);
+    constexpr bool G = !LSPG;   // Galerkin: pivoted solve, always out of shared memory
+    if (p.n == 40) return launch_wide_t<5, LSPG, true, G>(p, st);
+    if (p.n < 40) {
+        if (LSPG && p.n <= 33) return launch_wide_t<5, LSPG, false, true>(p, st);
+        return launch_wide_t<5, LSPG, false, G>(p, st);
+    }
+    if (p.n == 48) return launch_wide_t<6, LSPG, true, G>(p, st);
+    return launch_wide_t<6, LSPG, false, G>(p, st);
 }
 
 int launch_prom_wide(const PromParams &p, bool lspg, cudaStream_t st) {

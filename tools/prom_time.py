@@ -3,6 +3,8 @@ import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
 import burgers_b200
+if os.environ.get("BX_VARIANT_LIB"):   # experiments: a library built by tools/build_variant.sh
+    burgers_b200._lib.LIB_PATH = os.path.abspath(os.environ["BX_VARIANT_LIB"])
 from burgers_b200 import sweep
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
