@@ -44,6 +44,7 @@ SIGNATURES = {
     "bx_prom_workspace_bytes": (c_longlong, [c_int, c_int, c_int]),
     "bx_prom_trajectories": (c_int, [c_int, c_int, c_int, c_int, P, P, c_int, P, P, c_double, c_double,
                                      P, c_int, c_double, c_int, P, P, P, P, P]),
+    "bx_qm_decode": (c_int, [c_int, c_int, c_int, P, P, P, P, P, P]),
     "bx_reduced_system": (c_int, [c_int, c_int, c_int, P, P, P, P, P, c_double, c_double, c_int, P, c_longlong, c_int,
                                   P, P, P]),
     "bx_qm_workspace_bytes": (c_longlong, [c_int, c_int, c_int]),

@@ -279,6 +279,59 @@ class FEMBurgers:
                    "bx_fom_picard_trajectories")
         return U, iters
 
+    QM_FUSED_MAX_MODES = 31   # bx_qm_prom_trajectories (one fused trajectory kernel); larger bases go stepwise
+
+    def _qm_stepwise(self, At, nT, u0, batched, uxa, E, mu2, Phi, H, projection, U, iters, tol, itmax, eh):
+        """pod_quadratic_manifold (:1081-1175) for n > 31 modes (up to 128): the B samples advance in lock step, every
+        Gauss-Newton iteration is bx_qm_decode (u = Phi q + H sym(q x q) and T = Phi + H dQ/dq for all samples, :1116-1118,
+        :1148) + bx_reduced_system with T as a per-sample tangent and no SUPG term (:1141-1156) + one batched dense solve
+        (cuSOLVER; :1161).  A sample whose system is singular or whose state stops being finite carries iters = -1 and
+        NaN snapshots from that step on; the others are unaffected."""
+        lib = _lib.load()
+        B, N, n = U.shape[0], self.n_nodes, int(Phi.shape[1])
+        if n > 128:
+            raise _lib.BurgersB200Error(f"pod_quadratic_manifold: n = {n} modes > 128 is not supported by this build")
+        U[:, 0] = u0 if batched else u0.reshape(1, N)
+        q = self._new(B, n); u = self._new(B, N); T = self._new(B, N, n)
+        Ar = self._new(B, n, n); br = self._new(B, n)
+        bad = torch.zeros(B, dtype=torch.bool, device=self.device)
+
+        def decode():
+            _lib.check(lib.bx_qm_decode(B, N, n, _ptr(Phi), _ptr(H), _ptr(q), _ptr(u), _ptr(T), self._stream()),
+                       "bx_qm_decode")
+
+        for m in range(nT):
+            Um = U[:, m].contiguous()
+            Um_safe = torch.where(bad.unsqueeze(1), torch.zeros_like(Um), Um)
+            q.copy_(Um_safe @ Phi)                                                   # :1129
+            decode()
+            active = ~bad
+            count = torch.zeros(B, dtype=torch.int32, device=self.device)
+            for it in range(itmax):
+                self.reduced_system_batch(At, E, u, Um_safe, uxa, mu2, T, projection, supg=False, out=(Ar, br))
+                dq, info = torch.linalg.solve_ex(Ar, -br.unsqueeze(2))               # :1161
+                dq = dq.squeeze(2)
+                dq = torch.where(active.unsqueeze(1), dq, torch.zeros_like(dq))
+                q.add_(dq)                                                           # :1162
+                decode()                                                             # :1163 and the next tangent
+                rel = torch.linalg.norm(dq, dim=1) / torch.clamp(torch.linalg.norm(q, dim=1), min=1e-14)   # :1165
+                newly_bad = active & ((info != 0) | ~torch.isfinite(rel) | ~torch.isfinite(u).all(dim=1))
+                if eh is not None:
+                    eh[:, m, it] = torch.where(active, rel, eh[:, m, it])
+                count += active.to(torch.int32)
+                bad |= newly_bad
+                if bool(newly_bad.any()):
+                    q[newly_bad] = 0.0
+                active = active & ~(rel < tol) & ~bad
+                if not bool(active.any()):
+                    break
+            if bool(bad.any()):
+                u[bad] = float("nan")
+                count[bad] = -1
+            U[:, m + 1] = u
+            iters[:, m] = count
+        return U, iters
+
     @staticmethod
     def _projection_code(projection):
         """'Galerkin' / 'LSPG' exactly as the reference spells them (FEM/fem_burgers.py:754-764)."""
@@ -352,6 +405,9 @@ class FEMBurgers:
             raise ValueError("H must have shape (N, n(n+1)/2)")   # quadratic_prom_simulation.py:38
         if B == 0:
             return U, iters
+        if n > self.QM_FUSED_MAX_MODES:
+            return self._qm_stepwise(At, nT, u0, batched, uxa, E, mu2, Phi, H, "LSPG" if code == _lib.BX_LSPG else "Galerkin",
+                                     U, iters, float(newton_tol), int(newton_itmax), eh)
         lib = _lib.load()
         need = int(lib.bx_qm_workspace_bytes(B, N, n))
         if need < 0:

@@ -159,6 +159,13 @@ int bx_prom_trajectories(int B, int N, int n, int nsteps, const double *X, const
                          const double *Phi, int projection, double tol, int kmax,
                          double *U, int *iters, double *err_hist, void *workspace, void *stream);
 
+/* Decoder and tangent of the quadratic manifold for B reduced states (FEM/fem_burgers.py:263-312, 1116-1118, 1148):
+ * u = Phi q + H sym(q x q) -> u (B, N);  T = Phi + H dQ/dq -> T (B, N, n) (NULL: decoder only).  q: (B, n).
+ * n <= 128.  The stepwise quadratic-manifold path for n > 31 (bx_qm_prom_trajectories covers n <= 31) is built
+ * from this, bx_reduced_system (per-sample tangent, supg = 0) and a batched dense solve.                   */
+int bx_qm_decode(int B, int N, int n, const double *Phi, const double *H, const double *q, double *u, double *T,
+                 void *stream);
+
 /* The reduced system of ONE nonlinear iteration for a caller-supplied tangent: the block every
  * PROM variant of the reference repeats with its own decoder tangent in the place of Phi — pod_prom_burgers
  * FEM/fem_burgers.py:730-762, local_prom_burgers :1022-1058, pod_ann_prom :1225-1262, pod_rbf_prom :1330-1375,

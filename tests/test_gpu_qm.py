@@ -127,3 +127,49 @@ def test_manifold_builder_reproduces_reference_artifacts(golden, oracle):
     assert np.linalg.norm(Hs - g["H"]) <= 1e-11 * np.linalg.norm(g["H"])
     Qt = quadratic.sym_monomials_rows(torch.from_numpy(np.ascontiguousarray(g["q"].T)).cuda()).cpu().numpy()
     assert np.array_equal(Qt.T, g["Q"])
+
+
+@pytest.mark.parametrize("n,proj", [(32, "LSPG"), (40, "LSPG"), (40, "Galerkin"), (64, "LSPG")])
+def test_quadratic_manifold_beyond_31_modes_stepwise(n, proj, oracle):
+    """n > 31 modes (the reference method takes any n, FEM/fem_burgers.py:1081-1094; its mode-count heuristic,
+    build_quadratic_manifold.py:29-34, grows with the snapshot set): the stepwise path — bx_qm_decode + bx_reduced_system
+    with a per-sample tangent + a batched solve — against the oracle, plus the decoder / tangent kernel on its own."""
+    import burgers_b200
+    import torch
+    from conftest import GOLDEN, rel_l2_per_step
+    X, _ = oracle.mesh(512)
+    fem = burgers_b200.FEMBurgers(X)
+    m1, m2 = oracle.parameter_grid(3, 3)
+    Ut, _ = fem.fom_burgers_batch(0.05, 500, np.ones(512), m1, 0.0, m2)
+    S = np.ascontiguousarray(Ut.cpu().numpy().reshape(-1, 512).T)
+    Phi = np.ascontiguousarray(np.load(f"{GOLDEN}/Phi_tol_1e-04.npy")[:, :n])
+    q = Phi.T @ S
+    H = np.ascontiguousarray(oracle.compute_H(oracle.build_Q(q), oracle.build_E(S, Phi, q), 1e-2))
+    # decoder / tangent kernel alone
+    rng = np.random.default_rng(n)
+    qs = q[:, rng.integers(0, q.shape[1], 5)].T.copy()
+    lib = burgers_b200._lib.load()
+    dev = torch.device("cuda")
+    qd = torch.from_numpy(qs).to(dev); Pd = torch.from_numpy(Phi).to(dev); Hd = torch.from_numpy(H).to(dev)
+    ud = torch.empty((5, 512), dtype=torch.float64, device=dev); Td = torch.empty((5, 512, n), dtype=torch.float64, device=dev)
+    assert lib.bx_qm_decode(5, 512, n, Pd.data_ptr(), Hd.data_ptr(), qd.data_ptr(), ud.data_ptr(), Td.data_ptr(),
+                            torch.cuda.current_stream().cuda_stream) == 0
+    for b in range(5):
+        uo = Phi @ qs[b] + H @ oracle.sym_monomials(qs[b])
+        To = Phi + H @ oracle.dQ_dq(qs[b])
+        assert np.abs(ud[b].cpu().numpy() - uo).max() <= 1e-12 * np.abs(uo).max()
+        assert np.abs(Td[b].cpu().numpy() - To).max() <= 1e-11 * np.abs(To).max()
+    # trajectories
+    mu1 = np.array([4.3, 4.75, 5.4]); mu2 = np.array([0.016, 0.02, 0.029])
+    nT = 6
+    U, it = fem.pod_quadratic_manifold_batch(0.05, nT, np.ones(512), mu1, 0.0, mu2, Phi, H, proj)
+    U = U.cpu().numpy(); it = it.cpu().numpy()
+    Phi1 = np.nextafter(Phi, Phi + 1.0); H1 = np.nextafter(H, H + 1.0)
+    for b in range(3):
+        Uo, ito = oracle.pod_quadratic_manifold(X, 0.05, nT, np.ones(512), mu1[b], 0.0, mu2[b], Phi, H, proj)
+        Up, _ = oracle.pod_quadratic_manifold(X, 0.05, nT, np.ones(512), mu1[b], 0.0, mu2[b], Phi1, H1, proj)
+        sens = rel_l2_per_step(Up, Uo)        # the problem's own one-ulp sensitivity (see test_gpu_parity_full.py)
+        tol = max(1e-10, 20.0 * sens)
+        if sens <= 1e-8:
+            assert np.array_equal(it[b], ito), (b, it[b], ito)
+        assert rel_l2_per_step(U[b].T, Uo) <= tol, (b, sens)
