@@ -13,7 +13,7 @@ struct FomParams {
     const double *mu1;
     const double *mu2;
     double At, E, tol2;
-    double a6, c1;        // At / 6 (convection), 1.5 At (SUPG): kernel parameters so that they can stay in the constant bank
+    double a6, c1, c16;   // At / 6 (convection), 1.5 At and At / 4 (SUPG): kernel parameters so that they can stay in the constant bank
     double *U;
     int *iters;
     double *err_hist;     // optional (B, nsteps, kmax): |delta| / |U_{k+1}| after every iteration (:698)

@@ -70,7 +70,7 @@ __global__ void __launch_bounds__(32 * W, StrongShape<M, W>::MINB) fom_strong_ke
     double *s_off = smem;             // h/6 - At E / h   (off-diagonal constant of A; 0 where no element)
     double *s_h6 = s_off + L::EL;     // h/6
     double *s_dg = s_h6 + L::EL;      // diagonal constant of A (1 for padded rows)
-    double *w_hfs = s_dg + L::NL;     // (h/6) (f_gp1 + f_gp2) per element
+    double *w_hfs = s_dg + L::NL;     // 1.5 At (h/6) (f_gp1 + f_gp2) per element (bx_fom.cu)
     double *w_atf = w_hfs + L::EL;    // At * F per node
     double *w_bn = w_atf + L::NL;     // M U^n + At F per node (per time step)
     CondRow *x_row = reinterpret_cast<CondRow *>(w_bn + L::NL);
@@ -114,10 +114,9 @@ __global__ void __launch_bounds__(32 * W, StrongShape<M, W>::MINB) fom_strong_ke
     const bool vec_ok = (node0 + M <= N) && ((N & 1) == 0) && ((M & 1) == 0);
     const int jl = N - 1 - node0;   // local index of the last real row (see bx_fom.cu)
     const double a6 = At / 6.0;
-    const double c1 = 1.5 * At;
+    const double c1 = 1.5 * At, c16 = 0.25 * At;
     const bool leftv = gl > 0 && jl >= 0;
     const double a6L = leftv ? a6 : 0.0;
-    const double c1L = leftv ? c1 : 0.0;
 
     for (;;) {
         int s = 0;
@@ -149,7 +148,7 @@ __global__ void __launch_bounds__(32 * W, StrongShape<M, W>::MINB) fom_strong_ke
                     c0 = (f1 * BX_GA + f2 * BX_GB) * dV;
                     cr = (f1 * BX_GB + f2 * BX_GA) * dV;
                 }
-                w_hfs[(jj + 1) * LN + gl] = hfs;
+                w_hfs[(jj + 1) * LN + gl] = c1 * hfs;
                 if (jj >= 0) w_atf[jj * LN + gl] = At * (left + c0);
                 left = cr;
             }
@@ -192,8 +191,8 @@ __global__ void __launch_bounds__(32 * W, StrongShape<M, W>::MINB) fom_strong_ke
                 const double u1 = uL, u2 = u[0];
                 const double sm = u1 + u2;
                 qL = fma(a6L, u2, a6L * sm);
-                const double z = fma(sm * (u2 - u1), 1.0 / 6.0, -w_hfs[gl]);
-                GL = (c1L * rcp1(fmax(fabs(sm), 2.0e-10))) * z;
+                const double z = fma(sm * (u2 - u1), c16, -w_hfs[gl]);
+                GL = leftv ? rcp1(fmax(fabs(sm), 2.0e-10)) * z : 0.0;
                 offL = s_off[gl];
             }
 #pragma unroll
@@ -206,15 +205,15 @@ __global__ void __launch_bounds__(32 * W, StrongShape<M, W>::MINB) fom_strong_ke
                 const double t = a6 * sm;
                 double pe = fma(a6, u1, t);
                 double qe = fma(a6, u2, t);
-                const double z = fma(sm * (u2 - u1), 1.0 / 6.0, -w_hfs[ei]);
-                double Ge = (c1 * rcp1(fmax(fabs(sm), 2.0e-10))) * z;
+                const double z = fma(sm * (u2 - u1), c16, -w_hfs[ei]);
+                double Ge = rcp1(fmax(fabs(sm), 2.0e-10)) * z;
                 if ((!EXACT || j == M - 1) && j == jl) { pe = 0.0; qe = 0.0; Ge = 0.0; }
                 const double off = s_off[ei];
                 double a = offL - qL;
                 double c = off + pe;
                 double b = s_dg[j * LN + gl] + (qL - pe);
                 const double rhs = w_bn[j * LN + gl] - GL + Ge;
-                double r = rhs - fma(a, um, fma(b, u1, c * u2));
+                double r = rhs - fma(a, um, fma(b, u1, c * u2));   // (A U_k off the chain of the SUPG reciprocals)
                 if (j == 0 && gl == 0) { a = 0.0; b = 1.0; c = 0.0; r = mu1 - u1; }   // Dirichlet row (:679-680, :686)
                 ct.row(j, a, b, c, r, cs[j], rs[j], fs[j]);
                 offL = off; qL = qe; GL = Ge;
