@@ -65,11 +65,18 @@ def test_qm_config4_path_vs_oracle(n, proj, oracle, fem512, training_snapshots):
     rng = np.random.default_rng(n)
     Phi1 = np.nextafter(Phi, Phi + np.where(rng.random(Phi.shape) < 0.5, -1.0, 1.0))
     H1 = np.nextafter(H, H + np.where(rng.random(H.shape) < 0.5, -1.0, 1.0))
-    sens = np.zeros(QM_MU1.size)
-    for b in range(QM_MU1.size):
-        Ua, _ = oracle.pod_quadratic_manifold(X, 0.05, nT, np.ones(512), QM_MU1[b], 0.0, QM_MU2[b], Phi, H, proj)
-        Ub, _ = oracle.pod_quadratic_manifold(X, 0.05, nT, np.ones(512), QM_MU1[b], 0.0, QM_MU2[b], Phi1, H1, proj)
-        sens[b] = rel_l2_per_step(Ub, Ua)
+    def sensitivity(itmax):
+        out = np.zeros(QM_MU1.size)
+        for b in range(QM_MU1.size):
+            Ua, _ = oracle.pod_quadratic_manifold(X, 0.05, nT, np.ones(512), QM_MU1[b], 0.0, QM_MU2[b], Phi, H, proj, 1e-6, itmax)
+            Ub, _ = oracle.pod_quadratic_manifold(X, 0.05, nT, np.ones(512), QM_MU1[b], 0.0, QM_MU2[b], Phi1, H1, proj, 1e-6, itmax)
+            with np.errstate(all="ignore"):
+                r = rel_l2_per_step(Ub, Ua)
+            out[b] = r if np.isfinite(r) else np.inf
+        return out
+
+    sens_by_cap = {25: sensitivity(25), 6: sensitivity(6)}   # (the capped pass of n = 31 Galerkin diverges outright)
+    sens = sens_by_cap[25]
     tols = np.maximum(TOL, 20.0 * sens)   # per sample (n = 31 Galerkin: sens up to 4e-4 where the first steps run into
     #                                       newton_itmax without converging; kernel vs oracle stays below 20 x that)
     assert np.count_nonzero(sens <= 1e-6) >= 4, sens   # (n = 31 Galerkin: 5 of the 11 samples)
@@ -93,8 +100,10 @@ def test_qm_config4_path_vs_oracle(n, proj, oracle, fem512, training_snapshots):
             # capped pass: the Newton loop is cut after 6 iterations, before it has contracted, so the kappa * eps
             # differences between two summation orders mid-iteration are carried into the next step undamped:
             # 1e-8 there (as for the 500-step runs below), 1e-10 for the converged pass
+            sens = sens_by_cap[itmax]
+            tols = np.maximum(TOL, 20.0 * sens)
             for b, (Uo, ito) in enumerate(ref):
-                if sens[b] > 1e-6:    # not a determinate FP64 problem (n = 31 Galerkin, the samples whose first steps hit
+                if not (sens[b] <= 1e-6):    # not a determinate FP64 problem (n = 31 Galerkin, the samples whose first steps hit
                     continue          # newton_itmax without converging: counts differ between equally valid summation orders)
                 tol_pass = tols[b] if itmax == 25 else max(tols[b], 1e-8)
                 if sens[b] <= 1e-8:

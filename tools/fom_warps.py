@@ -4,6 +4,8 @@ import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
 import burgers_b200
+if os.environ.get("BX_VARIANT_LIB"):   # experiments: a library built by tools/build_variant.sh
+    burgers_b200._lib.LIB_PATH = os.path.abspath(os.environ["BX_VARIANT_LIB"])
 
 nsteps = int(sys.argv[1]) if len(sys.argv) > 1 else 500
 Bs = [int(x) for x in sys.argv[2:]] or [148, 296, 512, 888, 1024, 1776, 2048, 4096]
