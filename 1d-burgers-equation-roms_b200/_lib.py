@@ -36,6 +36,8 @@ SIGNATURES = {
     "bx_fom_plan": (c_int, [c_int, c_int]),
     "bx_fom_picard_trajectories": (c_int, [c_int, c_int, c_int, P, P, c_int, P, P, c_double, c_double,
                                            c_double, c_int, P, P, P, P, P]),
+    "bx_fom_picard_trajectories_noalloc": (c_int, [c_int, c_int, c_int, P, P, c_int, P, P, c_double, c_double,
+                                                   c_double, c_int, P, P, P, P]),
     "bx_fine_workspace_bytes": (c_longlong, [c_int]),
     "bx_fom_picard_finemesh": (c_int, [c_int, c_int, c_int, P, P, c_int, P, P, c_double, c_double,
                                        c_double, c_int, P, P, P, P]),

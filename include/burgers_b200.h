@@ -131,6 +131,19 @@ int bx_fom_picard_trajectories(int B, int N, int nsteps, const double *X, const 
                                double At, double E, double tol, int kmax,
                                double *U, int *iters, double *err_hist, void *workspace, void *stream);
 
+/* No counterpart in the reference.  bx_fom_picard_trajectories for
+ * callers that cannot allocate device memory (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc):
+ * same arguments, outputs and error behaviour, without the workspace — the scratch is a static device array inside
+ * the library (256 + 4 * BX_NOALLOC_MAX_TRAJECTORIES bytes, held by every GPU that loads the library until exit).
+ * B > BX_NOALLOC_MAX_TRAJECTORIES is rejected with BX_ERR_UNSUPPORTED.  The call allocates nothing (no cudaMalloc /
+ * cudaFree, no allocating library routine).  Every call on a device shares the array: calls that overlap on the GPU
+ * (two streams, two host threads) race — issue them one after the other on one stream, or use the workspace form. */
+#define BX_NOALLOC_MAX_TRAJECTORIES 65536
+int bx_fom_picard_trajectories_noalloc(int B, int N, int nsteps, const double *X, const double *u0,
+                                       int u0_batched, const double *mu1, const double *mu2,
+                                       double At, double E, double tol, int kmax,
+                                       double *U, int *iters, double *err_hist, void *stream);
+
 /* FEMBurgers.fom_burgers, FEM/fem_burgers.py:646-707, on a mesh too large for one warp (N > 1024;
  * BASELINE config 5: 2^20 nodes): one persistent cooperative kernel per call, the N x N tridiagonal solve
  * of every Picard iteration done by a three-level partition / cyclic-reduction method across threads,
