@@ -21,8 +21,18 @@
 // U_k lives in registers and the swept rows (cs, rs, fs) in shared memory (192 KB) for the whole
 // trajectory; mesh / forcing constants and M U^n + At F stream from an L2-resident scratch in a
 // [row][thread] interleaved layout (coalesced).  HBM traffic: the 8N-byte snapshot per time step.
+//
+// MULTI (bx_fom_picard_finemesh_ranks): the trajectory is cut once more, into R <= 8 contiguous node blocks, one per
+// GPU (one process per GPU), and the solve gets a FOURTH level: every CTA of a rank folds the rank's CTA rows into
+// ONE row + fgr (two group_up stages: 32 CTAs per warp, then the <= 5 groups), CTA 0 stores that row (7 doubles)
+// straight into every rank's exchange buffer through peer memory (NVLink; cudaIpc-mapped) and releases a flag, every
+// CTA acquires the R flags in its OWN buffer, solves the R-row closed system redundantly and walks back down.  A
+// second exchange of the same kind carries the norm partials (summed in rank order: every CTA of every rank takes
+// the same decision) and the block-edge states.  No collective library on the data path, no host round trip; the
+// state of a rank never leaves its GPU.  Meshes up to R x 148 x 8192 nodes.
 #include "bx_common.cuh"
 #include <cstdint>
+#include <cstring>
 
 namespace bx {
 
@@ -31,6 +41,14 @@ constexpr int FT = 512;           // threads per CTA
 constexpr int FW = FT / 32;       // warps per CTA
 constexpr int FNODES = FM * FT;   // nodes per CTA
 constexpr int FGMAX = 160;        // CTAs the top-level solve covers (5 rows per lane)
+constexpr int FRMAX = 8;          // ranks the rank-level solve covers
+
+// exchange buffer of a rank (peer-mapped by every other rank), byte offsets
+constexpr size_t PX_FLAGS = 0;        // u64 [2 kinds][FRMAX]: last epoch rank s has published for this kind
+constexpr size_t PX_FAIL = 128;       // u64: non-zero once any rank gave up waiting
+constexpr size_t PX_PAYLOAD = 256;    // double [2 parities][2 kinds][FRMAX][8]
+constexpr size_t PX_BYTES = 4096;
+constexpr unsigned long long PX_TIMEOUT_NS = 10ull * 1000ull * 1000ull * 1000ull;
 
 struct FineParams {
     int B, N, nsteps, kmax, G;
@@ -47,6 +65,10 @@ struct FineParams {
     double *g_rows;           // [G][8]: al, be, gaE, rho, F, G, R, -
     double *g_norm;           // [G][4]: sd, su, u_first, u_last
     unsigned long long *bar;
+    // MULTI only: this rank's node block [off, off + Nloc) of the N-node mesh; u0 / U / iters are the block's
+    int R, rank, off, Nloc;
+    unsigned long long seq;   // launch sequence number << 32: epochs of this launch are seq + 1, seq + 2, ...
+    char *peer[FRMAX];        // exchange buffer of every rank as mapped here ([rank] = own)
 };
 
 struct Lvl { double y, z1, z2; };
@@ -113,8 +135,11 @@ __device__ __forceinline__ Lvl group_up(int m, int lane, double &al, double &be,
 }
 
 // all CTAs of the (co-resident, cooperative) grid; monotonic 64-bit counter, target = epoch * G (two barriers per
-// Picard iteration and G arrivals each: a 32-bit counter would wrap after a few thousand trajectories per launch)
-__device__ __forceinline__ void grid_barrier(unsigned long long *bar, unsigned int G, unsigned long long &epoch) {
+// Picard iteration and G arrivals each: a 32-bit counter would wrap after a few thousand trajectories per launch).
+// MULTI: bar[16] is the rank's abort word (set when a wait on another rank timed out or a peer reported failure); a
+// CTA that sees it stops waiting and the barrier returns false — the CTA then leaves the kernel, so nothing can hang.
+template <bool MULTI>
+__device__ __forceinline__ bool grid_barrier(unsigned long long *bar, unsigned int G, unsigned long long &epoch, int *s_abort) {
     __syncthreads();
     if (threadIdx.x == 0) {
         ++epoch;
@@ -122,15 +147,80 @@ __device__ __forceinline__ void grid_barrier(unsigned long long *bar, unsigned i
         atomicAdd(bar, 1ull);
         const unsigned long long target = epoch * G;
         unsigned long long v;
+        bool aborted = false;
         do {
             asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(bar) : "memory");
+            if (MULTI && *reinterpret_cast<volatile unsigned long long *>(bar + 16) != 0ull) { aborted = true; break; }
         } while (v < target);
         __threadfence();
+        if (MULTI) *s_abort = aborted ? 1 : 0;
     }
     __syncthreads();
+    return MULTI ? (*s_abort == 0) : true;
 }
 
-__global__ void __launch_bounds__(FT, 1) fine_fom_kernel(const FineParams p) {
+// ---- peer-memory exchange between the ranks of a partitioned trajectory (MULTI) -------------------------
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *a) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long *a, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(a), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ size_t px_slot(unsigned long long ep, int kind, int src) {
+    return PX_PAYLOAD + sizeof(double) * 8 * ((((size_t)(ep & 1ull) * 2 + kind) * FRMAX) + src);
+}
+
+// lane s < R of ONE warp of the rank: store this rank's 8 values into rank s's buffer, then release the flag
+__device__ __forceinline__ void peer_publish(const FineParams &p, int kind, unsigned long long ep, int lane, const double (&v)[8]) {
+    if (lane < p.R) {
+        char *dst = p.peer[lane];
+        volatile double *pay = reinterpret_cast<volatile double *>(dst + px_slot(ep, kind, p.rank));
+#pragma unroll
+        for (int i = 0; i < 8; ++i) pay[i] = v[i];
+        __threadfence_system();
+        st_release_sys(reinterpret_cast<unsigned long long *>(dst + PX_FLAGS) + kind * FRMAX + p.rank, ep);
+    }
+}
+
+// one warp of every CTA: lane s < R waits for rank s's flag in the OWN buffer and reads its 8 values (lanes >= R: zeros).
+// A wait that exceeds PX_TIMEOUT_NS, or a failure word set by anybody, raises the failure word of every rank and this
+// rank's abort word; the values are then meaningless and the next grid barrier ends the kernel.
+__device__ __forceinline__ void peer_gather(const FineParams &p, int kind, unsigned long long ep, int lane, double (&v)[8]) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] = 0.0;
+    if (lane < p.R) {
+        char *own = p.peer[p.rank];
+        const unsigned long long *fl = reinterpret_cast<const unsigned long long *>(own + PX_FLAGS) + kind * FRMAX + lane;
+        volatile unsigned long long *failw = reinterpret_cast<volatile unsigned long long *>(own + PX_FAIL);
+        volatile unsigned long long *abortw = reinterpret_cast<volatile unsigned long long *>(p.bar + 16);
+        const unsigned long long t0 = global_timer_ns();
+        bool ok = true;
+        unsigned spins = 0;
+        while (ld_acquire_sys(fl) < ep) {
+            if (*failw != 0ull || *abortw != 0ull) { ok = false; break; }
+            if ((++spins & 1023u) == 0u && global_timer_ns() - t0 > PX_TIMEOUT_NS) { ok = false; break; }
+        }
+        if (!ok) {
+            for (int s = 0; s < p.R; ++s) *reinterpret_cast<volatile unsigned long long *>(p.peer[s] + PX_FAIL) = 1ull;
+            *abortw = 1ull;
+            __threadfence_system();
+        } else {
+            const double *pay = reinterpret_cast<const double *>(own + px_slot(ep, kind, lane));
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = __ldcv(pay + i);
+        }
+    }
+    __syncwarp();
+}
+
+template <bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_kernel(const FineParams p) {
     extern __shared__ __align__(16) double smem[];
     double *s_cs = smem;                    // swept rows of this thread: [j * FT + tid]
     double *s_rs = s_cs + FNODES;
@@ -141,16 +231,22 @@ __global__ void __launch_bounds__(FT, 1) fine_fom_kernel(const FineParams p) {
     double *s_wx = s_top + FGMAX + 2;       // [FW + 1]: x_last of warp w at [w + 1], [0] = CTA's P
     double *s_red = s_wx + FW + 2;          // [FW][4] norm partials / warp edge states
     double *s_dec = s_red + 4 * FW;         // [4]: sd, su, uL of the CTA, uR of the CTA
+    double *s_grp = s_dec + 4;              // MULTI: [5][8] rows + fgr of the groups of 32 CTAs
+    double *s_gx = s_grp + 40;              // MULTI: [6]: x_last of group g at [g + 1], [0] = the rank's P
+    int *s_abort = reinterpret_cast<int *>(s_gx + 8);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int cta = blockIdx.x, G = p.G, N = p.N;
-    const int node0 = (cta * FT + tid) * FM;
+    const int off = MULTI ? p.off : 0;       // first node of this rank's block
+    const int Nl = MULTI ? p.Nloc : N;       // nodes of the block (row length of u0 / U)
+    const int node0 = off + (cta * FT + tid) * FM;   // global node of the thread's first row
     const int jl = N - 1 - node0;           // local index of the last real row (may be outside [0, FM))
     const double At = p.At;
     const double a6 = At / 6.0, c1 = 1.5 * At;
     const bool has_e = p.E != 0.0;
     const double ate = At * p.E;
     unsigned long long epoch = 0;
+    unsigned long long xe0 = MULTI ? p.seq : 0ull, xe1 = xe0;   // epochs of the two kinds of exchange between ranks
 
     double *t_h6 = p.g_h6 + (size_t)cta * (FM + 1) * FT + tid;
     double *t_hfs = p.g_hfs + (size_t)cta * (FM + 1) * FT + tid;
@@ -193,20 +289,20 @@ __global__ void __launch_bounds__(FT, 1) fine_fom_kernel(const FineParams p) {
         }
         // ---- initial condition -> registers + snapshot 0 ---------------------------------------
         double u[FM];
-        double *Us = p.U + (long long)smp * (long long)(p.nsteps + 1) * N;
+        double *Us = p.U + (long long)smp * (long long)(p.nsteps + 1) * Nl;
         {
             const double *u0p = p.u0 + (long long)smp * p.u0_stride;
 #pragma unroll
             for (int j = 0; j < FM; ++j) {
-                u[j] = (node0 + j < N) ? u0p[node0 + j] : 0.0;
-                if (node0 + j < N) Us[node0 + j] = u[j];
+                u[j] = (node0 + j < N) ? u0p[node0 - off + j] : 0.0;
+                if (node0 + j < N) Us[node0 - off + j] = u[j];
             }
         }
         double sd = 0.0, su = 0.0, uL = 0.0, uR = 0.0;
 
         // publish partition-edge states (and norm partials), grid barrier, fetch neighbours' edges and
         // the grid-wide norms (summed in CTA order)
-        auto exchange = [&](double psd, double psu) {
+        auto exchange = [&](double psd, double psu) -> bool {
             warp_sum_pair(psd, psu);
             if (lane == 0) { s_red[4 * warp + 0] = psd; s_red[4 * warp + 1] = psu; s_red[4 * warp + 2] = u[0]; }
             if (lane == 31) s_red[4 * warp + 3] = u[FM - 1];
@@ -217,7 +313,7 @@ __global__ void __launch_bounds__(FT, 1) fine_fom_kernel(const FineParams p) {
                 double *gn = p.g_norm + 4 * cta;
                 gn[0] = a; gn[1] = b; gn[2] = s_red[2]; gn[3] = s_red[4 * (FW - 1) + 3];
             }
-            grid_barrier(p.bar, (unsigned)G, epoch);
+            if (!grid_barrier<MULTI>(p.bar, (unsigned)G, epoch, s_abort)) return false;
             if (warp == 0) {
                 // sum of G partials, fixed order: lane l takes CTAs 5 l .. 5 l + 4, then a butterfly
                 double a = 0.0, b = 0.0;
@@ -225,10 +321,28 @@ __global__ void __launch_bounds__(FT, 1) fine_fom_kernel(const FineParams p) {
                     a += __ldcg(p.g_norm + 4 * c); b += __ldcg(p.g_norm + 4 * c + 1);
                 }
                 warp_sum_pair(a, b);
+                double eL = 0.0, eR = 0.0;   // states just outside the rank's block
+                if (MULTI) {
+                    // the rank's partials and edge states go to every rank; the sums run in rank order
+                    ++xe1;
+                    double v[8];
+                    if (cta == 0) {
+                        v[0] = a; v[1] = b; v[2] = __ldcg(p.g_norm + 2); v[3] = __ldcg(p.g_norm + 4 * (G - 1) + 3);
+                        v[4] = v[5] = v[6] = v[7] = 0.0;
+                        peer_publish(p, 1, xe1, lane, v);
+                    }
+                    peer_gather(p, 1, xe1, lane, v);
+                    a = 0.0; b = 0.0;
+                    for (int r = 0; r < p.R; ++r) { a += shfl_idx(v[0], r); b += shfl_idx(v[1], r); }
+                    eL = shfl_idx(v[3], p.rank > 0 ? p.rank - 1 : 0);
+                    eR = shfl_idx(v[2], p.rank < p.R - 1 ? p.rank + 1 : p.rank);
+                    if (p.rank == 0) eL = 0.0;
+                    if (p.rank == p.R - 1) eR = 0.0;
+                }
                 if (lane == 0) {
                     s_dec[0] = a; s_dec[1] = b;
-                    s_dec[2] = cta > 0 ? __ldcg(p.g_norm + 4 * (cta - 1) + 3) : 0.0;
-                    s_dec[3] = cta < G - 1 ? __ldcg(p.g_norm + 4 * (cta + 1) + 2) : 0.0;
+                    s_dec[2] = cta > 0 ? __ldcg(p.g_norm + 4 * (cta - 1) + 3) : eL;
+                    s_dec[3] = cta < G - 1 ? __ldcg(p.g_norm + 4 * (cta + 1) + 2) : eR;
                 }
             }
             __syncthreads();
@@ -238,8 +352,9 @@ __global__ void __launch_bounds__(FT, 1) fine_fom_kernel(const FineParams p) {
             if (lane == 0) uL = warp > 0 ? s_red[4 * (warp - 1) + 3] : s_dec[2];
             if (lane == 31) uR = warp < FW - 1 ? s_red[4 * (warp + 1) + 2] : s_dec[3];
             __syncthreads();   // s_red / s_dec are rewritten by the next exchange
+            return true;
         };
-        exchange(0.0, 0.0);
+        if (!exchange(0.0, 0.0)) return;
 
         for (int n = 0; n < p.nsteps; ++n) {
             // ---- bn = M U^n + At F (constant during the Picard loop, :683) ---------------------
@@ -330,9 +445,69 @@ __global__ void __launch_bounds__(FT, 1) fine_fom_kernel(const FineParams p) {
                         d[0] = a2; d[1] = b2; d[2] = g2; d[3] = r2; d[4] = F2; d[5] = G2; d[6] = R2;
                     }
                 }
-                grid_barrier(p.bar, (unsigned)G, epoch);
+                if (!grid_barrier<MULTI>(p.bar, (unsigned)G, epoch, s_abort)) return;
+                if (MULTI) {
+                    // ================= rank level: fold the G rows of this rank, exchange, unfold ===========
+                    const int ng = (G + 31) >> 5;   // groups of 32 CTAs, one per warp
+                    Lvl l1; l1.y = 0.0; l1.z1 = 0.0; l1.z2 = 0.0;
+                    if (warp < ng) {
+                        const int c = 32 * warp + lane;
+                        double a3 = 0.0, b3 = 1.0, g3 = 0.0, r3 = 0.0, F3 = 0.0, G3 = 0.0, R3 = 0.0;
+                        if (c < G) {
+                            const double *d = p.g_rows + 8 * c;
+                            a3 = __ldcg(d); b3 = __ldcg(d + 1); g3 = __ldcg(d + 2); r3 = __ldcg(d + 3);
+                            F3 = __ldcg(d + 4); G3 = __ldcg(d + 5); R3 = __ldcg(d + 6);
+                        }
+                        const int m = G - 32 * warp < 32 ? G - 32 * warp : 32;
+                        l1 = group_up(m, lane, a3, b3, g3, r3, F3, G3, R3);
+                        if (lane == 0) {
+                            double *d = s_grp + 8 * warp;
+                            d[0] = a3; d[1] = b3; d[2] = g3; d[3] = r3; d[4] = F3; d[5] = G3; d[6] = R3;
+                        }
+                    }
+                    __syncthreads();
+                    if (warp == 0) {
+                        double a4 = 0.0, b4 = 1.0, g4 = 0.0, r4 = 0.0, F4 = 0.0, G4 = 0.0, R4 = 0.0;
+                        if (lane < ng) {
+                            const double *d = s_grp + 8 * lane;
+                            a4 = d[0]; b4 = d[1]; g4 = d[2]; r4 = d[3]; F4 = d[4]; G4 = d[5]; R4 = d[6];
+                        }
+                        const Lvl l2 = group_up(ng, lane, a4, b4, g4, r4, F4, G4, R4);   // -> the rank's row + fgr
+                        ++xe0;
+                        double v[8];
+                        if (cta == 0) {
+                            v[0] = a4; v[1] = b4; v[2] = g4; v[3] = r4; v[4] = F4; v[5] = G4; v[6] = R4; v[7] = 0.0;
+                            peer_publish(p, 0, xe0, lane, v);
+                        }
+                        peer_gather(p, 0, xe0, lane, v);
+                        // closed R-row system: one more group_up (lanes >= R hold identity rows), then the group's row
+                        // with nothing left (P = 0) or right (ga = 0) of the mesh gives x_last of the last rank
+                        double a5 = 0.0, b5 = 1.0, g5 = 0.0, r5 = 0.0, F5 = 0.0, G5 = 0.0, R5 = 0.0;
+                        if (lane < p.R) { a5 = v[0]; b5 = v[1]; g5 = v[2]; r5 = v[3]; F5 = v[4]; G5 = v[5]; R5 = v[6]; }
+                        const Lvl l3 = group_up(p.R, lane, a5, b5, g5, r5, F5, G5, R5);
+                        const double Xtop = r5 * rcp(b5);
+                        const double xr = fma(Xtop, l3.z2, l3.y);          // x_last of rank `lane`
+                        double Pr = shfl_idx(xr, p.rank > 0 ? p.rank - 1 : 0);
+                        if (p.rank == 0) Pr = 0.0;
+                        const double Xr = shfl_idx(xr, p.rank);
+                        if (lane < ng) s_gx[lane + 1] = fma(Xr, l2.z2, fma(-Pr, l2.z1, l2.y));
+                        if (lane == 0) s_gx[0] = Pr;
+                    }
+                    __syncthreads();
+                    if (warp < ng) {
+                        const double Pg = s_gx[warp], Xg = s_gx[warp + 1];
+                        if (32 * warp + lane < G) s_top[32 * warp + lane + 1] = fma(Xg, l1.z2, fma(-Pg, l1.z1, l1.y));
+                        if (warp == 0 && lane == 0) s_top[0] = Pg;
+                    }
+                    __syncthreads();
+                    if (warp == 0) {
+                        const double Pc = s_top[cta], Xc = s_top[cta + 1];
+                        if (lane < FW) s_wx[lane + 1] = fma(Xc, lc.z2, fma(-Pc, lc.z1, lc.y));
+                        if (lane == 0) s_wx[0] = Pc;
+                    }
+                }
                 // ================= grid level: closed G-row system, solved by every CTA ===========
-                if (warp == 0) {
+                if (!MULTI && warp == 0) {
                     constexpr int TM = FGMAX / 32;   // 5 rows per lane
                     double cs5[TM], rs5[TM], fs5[TM];
                     Continuant<TM> ct;
@@ -384,13 +559,13 @@ __global__ void __launch_bounds__(FT, 1) fine_fom_kernel(const FineParams p) {
                         psu = fma(u[j], u[j], psu);
                     }
                 }
-                exchange(psd, psu);
+                if (!exchange(psd, psu)) return;
                 ++k;
             } while (sd > p.tol2 * su && k < p.kmax);
 
             // ---- snapshot n+1 (:705) and iteration count -------------------------------------------
-            double *Un1 = Us + (long long)(n + 1) * N + node0;
-            if (node0 + FM <= N && ((N & 1) == 0)) {
+            double *Un1 = Us + (long long)(n + 1) * Nl + (node0 - off);
+            if (node0 + FM <= N && ((Nl & 1) == 0)) {
 #pragma unroll
                 for (int j = 0; j < FM; j += 2) *reinterpret_cast<double2 *>(Un1 + j) = make_double2(u[j], u[j + 1]);
             } else {
@@ -436,6 +611,47 @@ extern "C" long long bx_fine_workspace_bytes(int N) {
     return (long long)pl.total;
 }
 
+namespace bx {
+
+// shared launch: MULTI = false integrates the whole mesh on this device, MULTI = true this rank's node block
+template <bool MULTI>
+static int fine_launch(FineParams &p, void *workspace, cudaStream_t st) {
+    FinePlan pl;
+    fine_plan(MULTI ? p.Nloc : p.N, pl);
+    DeviceInfo di;
+    {
+        const int rcd = device_info(di);
+        if (rcd != BX_OK) return rcd;
+    }
+    const int sms = di.sms, coop = di.cooperative;
+    int occ = 0;
+    {
+        const int rco = kernel_occupancy(reinterpret_cast<const void *>(fine_fom_kernel<MULTI>), FT, FINE_SMEM, &occ);
+        if (rco != BX_OK) return rco;
+    }
+    if (!coop || occ < 1 || pl.G > sms * occ || pl.G > FGMAX) {
+        set_error("bx_fom_picard_finemesh: %d nodes need %d co-resident CTAs of %d nodes; this device runs %d",
+                  MULTI ? p.Nloc : p.N, pl.G, FNODES, (coop && occ >= 1) ? (sms * occ < FGMAX ? sms * occ : FGMAX) : 0);
+        return BX_ERR_UNSUPPORTED;
+    }
+    char *ws = static_cast<char *>(workspace);
+    p.G = pl.G;
+    p.bar = reinterpret_cast<unsigned long long *>(ws);
+    p.g_h6 = reinterpret_cast<double *>(ws + pl.off_h6);
+    p.g_hfs = reinterpret_cast<double *>(ws + pl.off_hfs);
+    p.g_atf = reinterpret_cast<double *>(ws + pl.off_atf);
+    p.g_bn = reinterpret_cast<double *>(ws + pl.off_bn);
+    p.g_rows = reinterpret_cast<double *>(ws + pl.off_rows);
+    p.g_norm = reinterpret_cast<double *>(ws + pl.off_norm);
+    BX_CUDA(cudaMemsetAsync(p.bar, 0, 256, st));
+    void *args[] = {&p};
+    BX_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void *>(fine_fom_kernel<MULTI>), dim3(pl.G), dim3(FT), args,
+                                        FINE_SMEM, st));
+    return BX_OK;
+}
+
+}  // namespace bx
+
 extern "C" int bx_fom_picard_finemesh(int B, int N, int nsteps, const double *X, const double *u0, int u0_batched,
                                       const double *mu1, const double *mu2, double At, double E, double tol,
                                       int kmax, double *U, int *iters, void *workspace, void *stream) {
@@ -445,41 +661,91 @@ extern "C" int bx_fom_picard_finemesh(int B, int N, int nsteps, const double *X,
     BX_REQUIRE(kmax >= 1, "kmax must be >= 1 (the reference loop body defines U1)");
     if (B == 0) return BX_OK;
     BX_REQUIRE(X && u0 && mu1 && mu2 && U && workspace, "null device pointer");
-    FinePlan pl;
-    fine_plan(N, pl);
-    DeviceInfo di;
-    {
-        const int rcd = device_info(di);
-        if (rcd != BX_OK) return rcd;
-    }
-    const int sms = di.sms, coop = di.cooperative;
-    int occ = 0;
-    {
-        const int rco = kernel_occupancy(reinterpret_cast<const void *>(fine_fom_kernel), FT, FINE_SMEM, &occ);
-        if (rco != BX_OK) return rco;
-    }
-    if (!coop || occ < 1 || pl.G > sms * occ || pl.G > FGMAX) {
-        set_error("bx_fom_picard_finemesh: N = %d needs %d co-resident CTAs of %d nodes; this device runs %d", N, pl.G,
-                  FNODES, (coop && occ >= 1) ? (sms * occ < FGMAX ? sms * occ : FGMAX) : 0);
-        return BX_ERR_UNSUPPORTED;
-    }
-    char *ws = static_cast<char *>(workspace);
-    FineParams p;
-    p.B = B; p.N = N; p.nsteps = nsteps; p.kmax = kmax; p.G = pl.G;
+    FineParams p = {};
+    p.B = B; p.N = N; p.nsteps = nsteps; p.kmax = kmax;
     p.X = X; p.u0 = u0; p.u0_stride = u0_batched ? N : 0;
     p.mu1 = mu1; p.mu2 = mu2; p.At = At; p.E = E; p.tol2 = tol * tol;
     p.U = U; p.iters = iters;
-    p.bar = reinterpret_cast<unsigned long long *>(ws);
-    p.g_h6 = reinterpret_cast<double *>(ws + pl.off_h6);
-    p.g_hfs = reinterpret_cast<double *>(ws + pl.off_hfs);
-    p.g_atf = reinterpret_cast<double *>(ws + pl.off_atf);
-    p.g_bn = reinterpret_cast<double *>(ws + pl.off_bn);
-    p.g_rows = reinterpret_cast<double *>(ws + pl.off_rows);
-    p.g_norm = reinterpret_cast<double *>(ws + pl.off_norm);
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    BX_CUDA(cudaMemsetAsync(p.bar, 0, 256, st));
-    void *args[] = {&p};
-    BX_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void *>(fine_fom_kernel), dim3(pl.G), dim3(FT), args,
-                                        FINE_SMEM, st));
+    p.R = 1; p.rank = 0; p.off = 0; p.Nloc = N;
+    return fine_launch<false>(p, workspace, static_cast<cudaStream_t>(stream));
+}
+
+// ---- the trajectory partitioned over R ranks (one process per GPU) ------------------------------------------
+extern "C" long long bx_fine_peer_bytes(void) { return (long long)bx::PX_BYTES; }
+
+// set-up calls (they allocate / map; not for the time-stepping loop): the exchange buffer has to come from cudaMalloc
+// itself so that its IPC handle maps the buffer and nothing else
+extern "C" int bx_peer_alloc(void **buf, void *ipc_handle_64_bytes) {
+    using namespace bx;
+    BX_REQUIRE(buf && ipc_handle_64_bytes, "null pointer");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    void *ptr = nullptr;
+    BX_CUDA(cudaMalloc(&ptr, PX_BYTES));
+    BX_CUDA(cudaMemset(ptr, 0, PX_BYTES));
+    cudaIpcMemHandle_t h;
+    BX_CUDA(cudaIpcGetMemHandle(&h, ptr));
+    memcpy(ipc_handle_64_bytes, &h, sizeof h);
+    *buf = ptr;
     return BX_OK;
+}
+extern "C" int bx_peer_open(const void *ipc_handle_64_bytes, void **buf) {
+    using namespace bx;
+    BX_REQUIRE(buf && ipc_handle_64_bytes, "null pointer");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, ipc_handle_64_bytes, sizeof h);
+    BX_CUDA(cudaIpcOpenMemHandle(buf, h, cudaIpcMemLazyEnablePeerAccess));
+    return BX_OK;
+}
+extern "C" int bx_peer_close(void *buf) {
+    using namespace bx;
+    BX_CUDA(cudaIpcCloseMemHandle(buf));
+    return BX_OK;
+}
+extern "C" int bx_peer_free(void *buf) {
+    using namespace bx;
+    BX_CUDA(cudaFree(buf));
+    return BX_OK;
+}
+
+extern "C" int bx_fom_picard_finemesh_ranks(int B, int N, int node_offset, int N_local, int nsteps, const double *X,
+                                            const double *u0_local, int u0_batched, const double *mu1, const double *mu2,
+                                            double At, double E, double tol, int kmax, double *U_local, int *iters,
+                                            void *workspace, int R, int rank, void *const *peer_bufs,
+                                            unsigned int launch_seq, void *stream) {
+    using namespace bx;
+    BX_REQUIRE(B >= 0 && nsteps >= 0, "B and nsteps must be non-negative");
+    BX_REQUIRE(N >= 2, "need at least 2 nodes (got N = %d)", N);
+    BX_REQUIRE(kmax >= 1, "kmax must be >= 1 (the reference loop body defines U1)");
+    BX_REQUIRE(R >= 1 && R <= FRMAX && rank >= 0 && rank < R, "1 <= R <= %d ranks, 0 <= rank < R (got R = %d, rank = %d)", FRMAX, R, rank);
+    BX_REQUIRE(N_local >= 1 && node_offset >= 0 && (long long)node_offset + N_local <= N, "node block [%d, %d + %d) outside the mesh", node_offset, node_offset, N_local);
+    BX_REQUIRE(node_offset % FNODES == 0, "node_offset must be a multiple of %d", FNODES);
+    BX_REQUIRE(node_offset + N_local == N || N_local % FNODES == 0, "every block but the last holds a multiple of %d nodes", FNODES);
+    BX_REQUIRE((rank == 0) == (node_offset == 0) && (rank == R - 1) == (node_offset + N_local == N), "blocks must be in rank order and cover the mesh");
+    BX_REQUIRE(launch_seq >= 1, "launch_seq starts at 1 and grows with every launch on these exchange buffers");
+    if (B == 0) return BX_OK;
+    BX_REQUIRE(X && u0_local && mu1 && mu2 && U_local && workspace && peer_bufs, "null pointer");
+    FineParams p = {};
+    p.B = B; p.N = N; p.nsteps = nsteps; p.kmax = kmax;
+    p.X = X; p.u0 = u0_local; p.u0_stride = u0_batched ? N_local : 0;
+    p.mu1 = mu1; p.mu2 = mu2; p.At = At; p.E = E; p.tol2 = tol * tol;
+    p.U = U_local; p.iters = iters;
+    p.R = R; p.rank = rank; p.off = node_offset; p.Nloc = N_local;
+    p.seq = (unsigned long long)launch_seq << 32;
+    for (int r = 0; r < R; ++r) {
+        BX_REQUIRE(peer_bufs[r] != nullptr, "peer_bufs[%d] is null", r);
+        p.peer[r] = static_cast<char *>(peer_bufs[r]);
+    }
+    return fine_launch<true>(p, workspace, static_cast<cudaStream_t>(stream));
+}
+
+// 1 when a rank gave up waiting for another one during a launch on this exchange buffer (the outputs of that launch
+// are then invalid on every rank), 0 otherwise; synchronises the stream
+extern "C" int bx_fine_peer_failed(const void *own_buf, void *stream) {
+    using namespace bx;
+    BX_REQUIRE(own_buf, "null pointer");
+    unsigned long long w = 0;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    BX_CUDA(cudaMemcpyAsync(&w, static_cast<const char *>(own_buf) + PX_FAIL, sizeof w, cudaMemcpyDeviceToHost, st));
+    BX_CUDA(cudaStreamSynchronize(st));
+    return w != 0ull ? 1 : 0;
 }
