@@ -4,7 +4,7 @@ from __future__ import annotations
 
 import ctypes
 import os
-from ctypes import c_char_p, c_double, c_int, c_longlong, c_uint, c_void_p
+from ctypes import c_char_p, c_double, c_int, c_longlong, c_void_p
 
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(PKG_DIR, "libburgers_b200.so")
@@ -47,7 +47,7 @@ SIGNATURES = {
     "bx_peer_close": (c_int, [P]),
     "bx_peer_free": (c_int, [P]),
     "bx_fom_picard_finemesh_ranks": (c_int, [c_int, c_int, c_int, c_int, c_int, P, P, c_int, P, P, c_double, c_double,
-                                             c_double, c_int, P, P, P, c_int, c_int, P, c_uint, P]),
+                                             c_double, c_int, P, P, P, c_int, c_int, P, P]),
     "bx_fine_peer_failed": (c_int, [P, P]),
     "bx_fom_newton_trajectories": (c_int, [c_int, c_int, c_int, P, P, c_int, P, P, c_double, c_double,
                                            c_double, c_double, c_int, P, P, P, P]),

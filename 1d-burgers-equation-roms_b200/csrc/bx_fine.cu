@@ -44,10 +44,11 @@ constexpr int FGMAX = 160;        // CTAs the top-level solve covers (5 rows per
 constexpr int FRMAX = 8;          // ranks the rank-level solve covers
 
 // exchange buffer of a rank (peer-mapped by every other rank), byte offsets
-constexpr size_t PX_FLAGS = 0;        // u64 [2 kinds][FRMAX]: last epoch rank s has published for this kind
+constexpr size_t PX_EPOCH = 0;        // u64: exchanges done on these buffers so far (kept by the kernels, the same on every rank)
 constexpr size_t PX_FAIL = 128;       // u64: non-zero once any rank gave up waiting
-constexpr size_t PX_PAYLOAD = 256;    // double [2 parities][2 kinds][FRMAX][8]
-constexpr size_t PX_BYTES = 4096;
+constexpr size_t PX_PAYLOAD = 256;    // u64 [2 parities][2 kinds][FRMAX sources][16 words]
+constexpr int PX_WORDS = 14;          // 7 doubles as 14 words of (32-bit epoch tag << 32 | 32 data bits)
+constexpr size_t PX_BYTES = 256 + 2 * 2 * FRMAX * 16 * 8;
 constexpr unsigned long long PX_TIMEOUT_NS = 10ull * 1000ull * 1000ull * 1000ull;
 
 struct FineParams {
@@ -67,7 +68,6 @@ struct FineParams {
     unsigned long long *bar;
     // MULTI only: this rank's node block [off, off + Nloc) of the N-node mesh; u0 / U / iters are the block's
     int R, rank, off, Nloc;
-    unsigned long long seq;   // launch sequence number << 32: epochs of this launch are seq + 1, seq + 2, ...
     char *peer[FRMAX];        // exchange buffer of every rank as mapped here ([rank] = own)
 };
 
@@ -160,61 +160,80 @@ __device__ __forceinline__ bool grid_barrier(unsigned long long *bar, unsigned i
 }
 
 // ---- peer-memory exchange between the ranks of a partitioned trajectory (MULTI) -------------------------
-__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *a) {
-    unsigned long long v;
-    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(a) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_release_sys(unsigned long long *a, unsigned long long v) {
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(a), "l"(v) : "memory");
-}
+// Each double travels as two 8-byte words that carry 32 data bits and the 32-bit epoch of the exchange: an aligned
+// 8-byte store arrives whole, so a word whose tag equals the expected epoch IS the data — no fence, no separate flag,
+// one NVLink crossing per exchange (the scheme NCCL calls LL).  Slots alternate with the parity of the epoch; a slot is
+// rewritten two exchanges of its kind later, which a rank can only reach after every rank has published the exchange in
+// between, i.e. after every CTA of every rank has read this one (a grid barrier lies between reading and publishing).
 __device__ __forceinline__ unsigned long long global_timer_ns() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     return t;
 }
-__device__ __forceinline__ size_t px_slot(unsigned long long ep, int kind, int src) {
-    return PX_PAYLOAD + sizeof(double) * 8 * ((((size_t)(ep & 1ull) * 2 + kind) * FRMAX) + src);
+__device__ __forceinline__ void st_sys_u64(unsigned long long *a, unsigned long long v) {
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(a), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_sys_u64(const unsigned long long *a) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ size_t px_slot(unsigned int ep, int kind, int src) {
+    return PX_PAYLOAD + 8 * 16 * ((((size_t)(ep & 1u) * 2 + kind) * FRMAX) + src);
 }
 
-// lane s < R of ONE warp of the rank: store this rank's 8 values into rank s's buffer, then release the flag
-__device__ __forceinline__ void peer_publish(const FineParams &p, int kind, unsigned long long ep, int lane, const double (&v)[8]) {
-    if (lane < p.R) {
-        char *dst = p.peer[lane];
-        volatile double *pay = reinterpret_cast<volatile double *>(dst + px_slot(ep, kind, p.rank));
+// ONE warp of the rank (all 32 lanes, v identical on every lane): word w of this rank's 7 values goes to every rank's
+// buffer, one store per (destination, word) spread over the lanes
+__device__ __forceinline__ void peer_publish(const FineParams &p, int kind, unsigned int ep, int lane, const double (&v)[8]) {
+    const int total = p.R * PX_WORDS;
+    for (int idx = lane; idx < total; idx += 32) {
+        const int dst = idx / PX_WORDS, w = idx - dst * PX_WORDS;
+        double d = v[0];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) pay[i] = v[i];
-        __threadfence_system();
-        st_release_sys(reinterpret_cast<unsigned long long *>(dst + PX_FLAGS) + kind * FRMAX + p.rank, ep);
+        for (int i = 1; i < 7; ++i) d = (w >> 1) == i ? v[i] : d;
+        const unsigned int half = (w & 1) ? (unsigned int)__double2hiint(d) : (unsigned int)__double2loint(d);
+        unsigned long long *slot = reinterpret_cast<unsigned long long *>(p.peer[dst] + px_slot(ep, kind, p.rank));
+        st_sys_u64(slot + w, ((unsigned long long)ep << 32) | half);
     }
 }
 
-// one warp of every CTA: lane s < R waits for rank s's flag in the OWN buffer and reads its 8 values (lanes >= R: zeros).
-// A wait that exceeds PX_TIMEOUT_NS, or a failure word set by anybody, raises the failure word of every rank and this
-// rank's abort word; the values are then meaningless and the next grid barrier ends the kernel.
-__device__ __forceinline__ void peer_gather(const FineParams &p, int kind, unsigned long long ep, int lane, double (&v)[8]) {
+// one warp of every CTA: lane s < R waits until the 14 words of rank s in the OWN buffer carry this epoch and unpacks its
+// 7 values (v[7] = 0; lanes >= R: zeros).  A wait that exceeds PX_TIMEOUT_NS, or a failure word set by anybody, raises the
+// failure word of every rank and this rank's abort word; the values are then meaningless and the next grid barrier
+// ends the kernel.
+__device__ __forceinline__ void peer_gather(const FineParams &p, int kind, unsigned int ep, int lane, double (&v)[8]) {
 #pragma unroll
     for (int i = 0; i < 8; ++i) v[i] = 0.0;
     if (lane < p.R) {
         char *own = p.peer[p.rank];
-        const unsigned long long *fl = reinterpret_cast<const unsigned long long *>(own + PX_FLAGS) + kind * FRMAX + lane;
+        const unsigned long long *slot = reinterpret_cast<const unsigned long long *>(own + px_slot(ep, kind, lane));
         volatile unsigned long long *failw = reinterpret_cast<volatile unsigned long long *>(own + PX_FAIL);
         volatile unsigned long long *abortw = reinterpret_cast<volatile unsigned long long *>(p.bar + 16);
-        const unsigned long long t0 = global_timer_ns();
+        unsigned long long t0 = 0ull;
         bool ok = true;
         unsigned spins = 0;
-        while (ld_acquire_sys(fl) < ep) {
-            if (*failw != 0ull || *abortw != 0ull) { ok = false; break; }
-            if ((++spins & 1023u) == 0u && global_timer_ns() - t0 > PX_TIMEOUT_NS) { ok = false; break; }
+        unsigned long long wd[PX_WORDS];
+        for (;;) {
+            bool all = true;
+#pragma unroll
+            for (int w = 0; w < PX_WORDS; ++w) wd[w] = ld_sys_u64(slot + w);
+#pragma unroll
+            for (int w = 0; w < PX_WORDS; ++w) all = all && (unsigned int)(wd[w] >> 32) == ep;
+            if (all) break;
+            if ((++spins & 63u) == 0u) {
+                if (*failw != 0ull || *abortw != 0ull) { ok = false; break; }
+                const unsigned long long t = global_timer_ns();
+                if (t0 == 0ull) t0 = t;
+                if (t - t0 > PX_TIMEOUT_NS) { ok = false; break; }
+            }
         }
         if (!ok) {
             for (int s = 0; s < p.R; ++s) *reinterpret_cast<volatile unsigned long long *>(p.peer[s] + PX_FAIL) = 1ull;
             *abortw = 1ull;
             __threadfence_system();
         } else {
-            const double *pay = reinterpret_cast<const double *>(own + px_slot(ep, kind, lane));
 #pragma unroll
-            for (int i = 0; i < 8; ++i) v[i] = __ldcv(pay + i);
+            for (int i = 0; i < 7; ++i) v[i] = __hiloint2double((int)(unsigned int)wd[2 * i + 1], (int)(unsigned int)wd[2 * i]);
         }
     }
     __syncwarp();
@@ -246,7 +265,13 @@ template <bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_kernel(c
     const bool has_e = p.E != 0.0;
     const double ate = At * p.E;
     unsigned long long epoch = 0;
-    unsigned long long xe0 = MULTI ? p.seq : 0ull, xe1 = xe0;   // epochs of the two kinds of exchange between ranks
+    // epochs of the two kinds of exchange between ranks: they continue where the last launch on these buffers stopped
+    unsigned int xe0 = 0u, xe1 = 0u;
+    if (MULTI) {
+        const volatile unsigned long long *ew = reinterpret_cast<const volatile unsigned long long *>(p.peer[p.rank] + PX_EPOCH);
+        xe0 = (unsigned int)ew[0];
+        xe1 = (unsigned int)ew[1];
+    }
 
     double *t_h6 = p.g_h6 + (size_t)cta * (FM + 1) * FT + tid;
     double *t_hfs = p.g_hfs + (size_t)cta * (FM + 1) * FT + tid;
@@ -578,6 +603,10 @@ template <bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_kernel(c
                 p.iters[(long long)smp * p.nsteps + n] = (su <= 1.7976931348623157e308) ? k : -1;
         }
     }
+    if (MULTI && cta == 0 && tid == 0) {   // the next launch on these buffers continues the epochs
+        volatile unsigned long long *ew = reinterpret_cast<volatile unsigned long long *>(p.peer[p.rank] + PX_EPOCH);
+        ew[0] = xe0; ew[1] = xe1;
+    }
 }
 
 constexpr size_t FINE_SMEM = sizeof(double) * (3 * (size_t)FNODES + 512);
@@ -710,8 +739,7 @@ extern "C" int bx_peer_free(void *buf) {
 extern "C" int bx_fom_picard_finemesh_ranks(int B, int N, int node_offset, int N_local, int nsteps, const double *X,
                                             const double *u0_local, int u0_batched, const double *mu1, const double *mu2,
                                             double At, double E, double tol, int kmax, double *U_local, int *iters,
-                                            void *workspace, int R, int rank, void *const *peer_bufs,
-                                            unsigned int launch_seq, void *stream) {
+                                            void *workspace, int R, int rank, void *const *peer_bufs, void *stream) {
     using namespace bx;
     BX_REQUIRE(B >= 0 && nsteps >= 0, "B and nsteps must be non-negative");
     BX_REQUIRE(N >= 2, "need at least 2 nodes (got N = %d)", N);
@@ -721,7 +749,6 @@ extern "C" int bx_fom_picard_finemesh_ranks(int B, int N, int node_offset, int N
     BX_REQUIRE(node_offset % FNODES == 0, "node_offset must be a multiple of %d", FNODES);
     BX_REQUIRE(node_offset + N_local == N || N_local % FNODES == 0, "every block but the last holds a multiple of %d nodes", FNODES);
     BX_REQUIRE((rank == 0) == (node_offset == 0) && (rank == R - 1) == (node_offset + N_local == N), "blocks must be in rank order and cover the mesh");
-    BX_REQUIRE(launch_seq >= 1, "launch_seq starts at 1 and grows with every launch on these exchange buffers");
     if (B == 0) return BX_OK;
     BX_REQUIRE(X && u0_local && mu1 && mu2 && U_local && workspace && peer_bufs, "null pointer");
     FineParams p = {};
@@ -730,7 +757,6 @@ extern "C" int bx_fom_picard_finemesh_ranks(int B, int N, int node_offset, int N
     p.mu1 = mu1; p.mu2 = mu2; p.At = At; p.E = E; p.tol2 = tol * tol;
     p.U = U_local; p.iters = iters;
     p.R = R; p.rank = rank; p.off = node_offset; p.Nloc = N_local;
-    p.seq = (unsigned long long)launch_seq << 32;
     for (int r = 0; r < R; ++r) {
         BX_REQUIRE(peer_bufs[r] != nullptr, "peer_bufs[%d] is null", r);
         p.peer[r] = static_cast<char *>(peer_bufs[r]);

@@ -47,7 +47,6 @@ class PeerExchange:
     def __init__(self, rank, bufs, own, opened):
         self.rank, self.bufs, self.own, self._opened = rank, list(bufs), own, opened
         self.R = len(self.bufs)
-        self.launch_seq = 0
         self.last_kernel_ms = None
 
     @classmethod
@@ -127,7 +126,6 @@ def fom_burgers_partitioned(X, At, nTimeSteps, u0_local, mu1, E, mu2, exchange: 
     iters = torch.empty((B, nT), dtype=torch.int32, device=dev)
     ws = torch.empty(int(lib.bx_fine_workspace_bytes(Nl)), dtype=torch.uint8, device=dev)
     stream = torch.cuda.current_stream(dev)
-    exchange.launch_seq += 1
     torch.cuda.synchronize(dev)
     if dist.is_initialized():
         dist.barrier(group)   # every rank is about to launch: the in-kernel waits are short
@@ -136,7 +134,7 @@ def fom_burgers_partitioned(X, At, nTimeSteps, u0_local, mu1, E, mu2, exchange: 
     _lib.check(lib.bx_fom_picard_finemesh_ranks(B, N, off, Nl, nT, Xd.data_ptr(), u0d.data_ptr(), batched, m1.data_ptr(),
                                                 m2.data_ptr(), float(At), float(E), float(tol), int(kmax), U.data_ptr(),
                                                 iters.data_ptr(), ws.data_ptr(), R, rank, exchange.pointer_array(),
-                                                exchange.launch_seq, stream.cuda_stream),
+                                                stream.cuda_stream),
                "bx_fom_picard_finemesh_ranks")
     e1.record(stream)
     if exchange.failed(stream.cuda_stream):

@@ -162,14 +162,14 @@ int bx_fom_picard_finemesh(int B, int N, int nsteps, const double *X, const doub
  * partition method of bx_fom_picard_finemesh with a fourth level: each rank condenses its block to one interface
  * row, stores it into every rank's exchange buffer through peer memory (NVLink) and solves the R-row closed system
  * redundantly; a second exchange carries the norm partials and the block-edge states.  No host round trip and no
- * collective library inside the launch: all ranks must launch (same B, N, nsteps, tol, kmax, launch_seq), the kernels
- * wait for each other on the device.
+ * collective library inside the launch: all ranks must launch (same B, N, nsteps, tol, kmax, the same sequence of
+ * launches on a set of exchange buffers), the kernels wait for each other on the device.
  * X: the WHOLE mesh (N).  u0_local: (N_local,) or (B, N_local).  U_local: (B, nsteps+1, N_local).  iters: (B, nsteps) or
  * NULL, identical on every rank.  workspace: bx_fine_workspace_bytes(N_local) bytes.
  * peer_bufs: host array of R device pointers, [r] = rank r's exchange buffer as mapped in this process ([rank] = own).
- * launch_seq: >= 1, strictly increasing over the launches that use these exchange buffers, the same on every rank.
- * A rank that waits more than 10 s for another one gives up: every rank's launch then ends early with invalid
- * outputs and bx_fine_peer_failed returns 1 (nothing hangs).                                                     */
+ * The exchange buffers carry an epoch counter from launch to launch (2^32 exchanges = 2^31 Picard iterations per
+ * set of buffers).  A rank that waits more than 10 s for another one gives up: every rank's launch then ends early
+ * with invalid outputs, bx_fine_peer_failed returns 1 (nothing hangs) and the buffers have to be re-created.        */
 long long bx_fine_peer_bytes(void);
 /* set-up (these four allocate / map device memory; call them outside the time-stepping loop): an exchange buffer of
  * bx_fine_peer_bytes() zeroed bytes from cudaMalloc + its 64-byte cudaIpcMemHandle_t; map / unmap another rank's.  */
@@ -180,8 +180,7 @@ int bx_peer_free(void *buf);
 int bx_fom_picard_finemesh_ranks(int B, int N, int node_offset, int N_local, int nsteps, const double *X,
                                  const double *u0_local, int u0_batched, const double *mu1, const double *mu2,
                                  double At, double E, double tol, int kmax, double *U_local, int *iters,
-                                 void *workspace, int R, int rank, void *const *peer_bufs,
-                                 unsigned int launch_seq, void *stream);
+                                 void *workspace, int R, int rank, void *const *peer_bufs, void *stream);
 /* 1 when a launch on this exchange buffer gave up waiting for another rank, else 0; synchronises the stream */
 int bx_fine_peer_failed(const void *own_buf, void *stream);
 

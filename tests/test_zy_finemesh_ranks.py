@@ -16,8 +16,9 @@ pytestmark = pytest.mark.gpu
 TOL = 1e-10
 
 
-def _run_ranks(X, At, nsteps, u0, mu1, E, mu2, R):
-    """R rank launches on R streams of cuda:0; returns the assembled (N, nsteps + 1) trajectory and the counts."""
+def _run_ranks(X, At, nsteps, u0, mu1, E, mu2, R, launches=1):
+    """R rank launches on R streams of cuda:0 (`launches` times on the same exchange buffers: the epochs carry over);
+    returns the assembled (N, nsteps + 1) trajectory and the counts."""
     import torch
     from burgers_b200 import _lib
     from burgers_b200.finemesh_dist import PeerExchange, node_partition
@@ -39,12 +40,12 @@ def _run_ranks(X, At, nsteps, u0, mu1, E, mu2, R):
             ws = torch.empty(int(lib.bx_fine_workspace_bytes(cnt)), dtype=torch.uint8, device=dev)
             keep.append((u0d, U, it, ws))
         torch.cuda.synchronize(dev)
-        for r, (off, cnt) in enumerate(parts):
+        for r, (off, cnt) in [pr for _ in range(launches) for pr in enumerate(parts)]:
             u0d, U, it, ws = keep[r]
             _lib.check(lib.bx_fom_picard_finemesh_ranks(1, N, off, cnt, nsteps, Xd.data_ptr(), u0d.data_ptr(), 0,
                                                         m1.data_ptr(), m2.data_ptr(), float(At), float(E), 1e-6, 20,
                                                         U.data_ptr(), it.data_ptr(), ws.data_ptr(), R, r,
-                                                        ex[r].pointer_array(), 1, streams[r].cuda_stream),
+                                                        ex[r].pointer_array(), streams[r].cuda_stream),
                        "bx_fom_picard_finemesh_ranks")
         torch.cuda.synchronize(dev)
         if any(e.failed(streams[r].cuda_stream) for r, e in enumerate(ex)):
@@ -66,7 +67,7 @@ def test_ranks_vs_oracle_and_single_kernel(N, R, oracle):
     X = np.linspace(0.0, 100.0, N)
     At = 0.05 * 511.0 / (N - 1)
     u0 = np.ones(N)
-    U, it = _run_ranks(X, At, 12, u0, 4.75, 0.0, 0.02, R)
+    U, it = _run_ranks(X, At, 12, u0, 4.75, 0.0, 0.02, R, launches=3 if R == 2 else 1)
     Uo, ito = oracle.fom_burgers(X, At, 12, u0, 4.75, 0.0, 0.02)
     assert np.array_equal(it, ito), (it, ito)
     assert rel_l2_per_step(U, Uo) <= TOL
@@ -92,11 +93,11 @@ def test_ranks_two_groups_of_ctas_nonuniform_mesh_diffusion(oracle):
 def test_ranks_argument_checks():
     from burgers_b200 import _lib
     lib = _lib.load()
-    # block offsets that are not multiples of 8192, more than 8 ranks, launch_seq 0
+    # block offsets that are not multiples of 8192, more than 8 ranks, a middle block that is not whole CTA blocks
     assert lib.bx_fom_picard_finemesh_ranks(1, 100000, 100, 1000, 1, None, None, 0, None, None, 0.05, 0.0, 1e-6, 20,
-                                            None, None, None, 2, 1, None, 1, None) == _lib.BX_ERR_INVALID
+                                            None, None, None, 2, 1, None, None) == _lib.BX_ERR_INVALID
     assert lib.bx_fom_picard_finemesh_ranks(1, 100000, 0, 8192, 1, None, None, 0, None, None, 0.05, 0.0, 1e-6, 20,
-                                            None, None, None, 9, 0, None, 1, None) == _lib.BX_ERR_INVALID
-    assert lib.bx_fom_picard_finemesh_ranks(1, 100000, 0, 8192, 1, None, None, 0, None, None, 0.05, 0.0, 1e-6, 20,
-                                            None, None, None, 2, 0, None, 0, None) == _lib.BX_ERR_INVALID
-    assert b"launch_seq" in lib.bx_last_error()
+                                            None, None, None, 9, 0, None, None) == _lib.BX_ERR_INVALID
+    assert lib.bx_fom_picard_finemesh_ranks(1, 100000, 0, 8000, 1, None, None, 0, None, None, 0.05, 0.0, 1e-6, 20,
+                                            None, None, None, 2, 0, None, None) == _lib.BX_ERR_INVALID
+    assert b"8192" in lib.bx_last_error()
