@@ -15,7 +15,7 @@ BX_PROBE_DFMA, BX_PROBE_DMMA = 0, 1
 # bx_set_tuning knobs (include/burgers_b200.h)
 TUNING_KNOBS = {"fom_warps_per_trajectory": 0, "prom_cta_warps": 1, "prom_cta_chunk": 2, "qm_schedule": 3,
                 "prom_warps_per_trajectory": 4, "fom_kernel": 5,
-                "fom_segment_steps": 6, "qm_group": 7}
+                "fom_segment_steps": 6, "qm_group": 7, "fine_rows": 8}
 
 P = c_void_p  # device pointer / stream
 

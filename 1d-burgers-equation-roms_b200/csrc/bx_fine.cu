@@ -36,10 +36,10 @@
 
 namespace bx {
 
-constexpr int FM = 16;            // nodes per thread
+constexpr int FM_MAX = 16;        // nodes per thread: 16 (8192 nodes per CTA), 8 or 4 — the fewest that keep the CTAs co-resident
 constexpr int FT = 512;           // threads per CTA
 constexpr int FW = FT / 32;       // warps per CTA
-constexpr int FNODES = FM * FT;   // nodes per CTA
+constexpr int FBLOCK = FM_MAX * FT;   // granularity of the node blocks of a partitioned trajectory
 constexpr int FGMAX = 160;        // CTAs the top-level solve covers (5 rows per lane)
 constexpr int FRMAX = 8;          // ranks the rank-level solve covers
 
@@ -239,7 +239,8 @@ __device__ __forceinline__ void peer_gather(const FineParams &p, int kind, unsig
     __syncwarp();
 }
 
-template <bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_kernel(const FineParams p) {
+template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_kernel(const FineParams p) {
+    constexpr int FNODES = FM * FT;   // nodes per CTA
     extern __shared__ __align__(16) double smem[];
     double *s_cs = smem;                    // swept rows of this thread: [j * FT + tid]
     double *s_rs = s_cs + FNODES;
@@ -609,21 +610,22 @@ template <bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_kernel(c
     }
 }
 
-constexpr size_t FINE_SMEM = sizeof(double) * (3 * (size_t)FNODES + 512);
+constexpr size_t fine_smem(int fm) { return sizeof(double) * (3 * (size_t)fm * FT + 512); }
 
 struct FinePlan {
     int G;
     size_t off_h6, off_hfs, off_atf, off_bn, off_rows, off_norm, total;
 };
 
-static int fine_plan(int N, FinePlan &pl) {
-    pl.G = (N + FNODES - 1) / FNODES;
+static int fine_plan(int N, int fm, FinePlan &pl) {
+    const int nodes = fm * FT;
+    pl.G = (N + nodes - 1) / nodes;
     size_t o = 256;
     auto take = [&](size_t doubles) { size_t at = o; o += sizeof(double) * doubles; o = (o + 255) & ~(size_t)255; return at; };
-    pl.off_h6 = take((size_t)pl.G * (FM + 1) * FT);
-    pl.off_hfs = take((size_t)pl.G * (FM + 1) * FT);
-    pl.off_atf = take((size_t)pl.G * FNODES);
-    pl.off_bn = take((size_t)pl.G * FNODES);
+    pl.off_h6 = take((size_t)pl.G * (fm + 1) * FT);
+    pl.off_hfs = take((size_t)pl.G * (fm + 1) * FT);
+    pl.off_atf = take((size_t)pl.G * nodes);
+    pl.off_bn = take((size_t)pl.G * nodes);
     pl.off_rows = take((size_t)(pl.G + 1) * 8);
     pl.off_norm = take((size_t)pl.G * 4);
     pl.total = o;
@@ -635,32 +637,32 @@ static int fine_plan(int N, FinePlan &pl) {
 extern "C" long long bx_fine_workspace_bytes(int N) {
     using namespace bx;
     if (N < 2) return -1;
-    FinePlan pl;
-    fine_plan(N, pl);
-    return (long long)pl.total;
+    size_t most = 0;
+    for (int fm = 4; fm <= FM_MAX; fm *= 2) {
+        FinePlan pl;
+        fine_plan(N, fm, pl);
+        most = pl.total > most ? pl.total : most;
+    }
+    return (long long)most;
 }
 
 namespace bx {
 
-// shared launch: MULTI = false integrates the whole mesh on this device, MULTI = true this rank's node block
-template <bool MULTI>
-static int fine_launch(FineParams &p, void *workspace, cudaStream_t st) {
+// one instance: MULTI = false integrates the whole mesh on this device, MULTI = true this rank's node block.
+// probe: return 1 instead of an error when the CTAs of this instance cannot all be resident
+template <int FM, bool MULTI>
+static int fine_launch_rows(FineParams &p, void *workspace, cudaStream_t st, int limit, bool probe) {
     FinePlan pl;
-    fine_plan(MULTI ? p.Nloc : p.N, pl);
-    DeviceInfo di;
-    {
-        const int rcd = device_info(di);
-        if (rcd != BX_OK) return rcd;
-    }
-    const int sms = di.sms, coop = di.cooperative;
+    fine_plan(MULTI ? p.Nloc : p.N, FM, pl);
     int occ = 0;
     {
-        const int rco = kernel_occupancy(reinterpret_cast<const void *>(fine_fom_kernel<MULTI>), FT, FINE_SMEM, &occ);
+        const int rco = kernel_occupancy(reinterpret_cast<const void *>(fine_fom_kernel<FM, MULTI>), FT, fine_smem(FM), &occ);
         if (rco != BX_OK) return rco;
     }
-    if (!coop || occ < 1 || pl.G > sms * occ || pl.G > FGMAX) {
+    if (occ < 1 || pl.G > limit || pl.G > FGMAX) {
+        if (probe) return 1;
         set_error("bx_fom_picard_finemesh: %d nodes need %d co-resident CTAs of %d nodes; this device runs %d",
-                  MULTI ? p.Nloc : p.N, pl.G, FNODES, (coop && occ >= 1) ? (sms * occ < FGMAX ? sms * occ : FGMAX) : 0);
+                  MULTI ? p.Nloc : p.N, pl.G, FM * FT, occ >= 1 ? (limit < FGMAX ? limit : FGMAX) : 0);
         return BX_ERR_UNSUPPORTED;
     }
     char *ws = static_cast<char *>(workspace);
@@ -674,9 +676,33 @@ static int fine_launch(FineParams &p, void *workspace, cudaStream_t st) {
     p.g_norm = reinterpret_cast<double *>(ws + pl.off_norm);
     BX_CUDA(cudaMemsetAsync(p.bar, 0, 256, st));
     void *args[] = {&p};
-    BX_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void *>(fine_fom_kernel<MULTI>), dim3(pl.G), dim3(FT), args,
-                                        FINE_SMEM, st));
+    BX_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void *>(fine_fom_kernel<FM, MULTI>), dim3(pl.G), dim3(FT), args,
+                                        fine_smem(FM), st));
     return BX_OK;
+}
+
+// rows per thread: the fewest (4, 8, 16) whose CTAs are all co-resident, one per SM — a Picard iteration is a chain of
+// latencies (two grid barriers, three group solves) plus the thread-level sweep, which shrinks with the rows per thread;
+// BX_TUNE_FINE_ROWS forces a value
+template <bool MULTI>
+static int fine_launch(FineParams &p, void *workspace, cudaStream_t st) {
+    DeviceInfo di;
+    {
+        const int rcd = device_info(di);
+        if (rcd != BX_OK) return rcd;
+    }
+    if (!di.cooperative) {
+        set_error("bx_fom_picard_finemesh: the device does not support cooperative launches");
+        return BX_ERR_UNSUPPORTED;
+    }
+    const int forced = tuning(BX_TUNE_FINE_ROWS);
+    if (forced == 4) return fine_launch_rows<4, MULTI>(p, workspace, st, di.sms, false);
+    if (forced == 8) return fine_launch_rows<8, MULTI>(p, workspace, st, di.sms, false);
+    if (forced == 16) return fine_launch_rows<16, MULTI>(p, workspace, st, di.sms, false);
+    int rc = fine_launch_rows<4, MULTI>(p, workspace, st, di.sms, true);
+    if (rc == 1) rc = fine_launch_rows<8, MULTI>(p, workspace, st, di.sms, true);
+    if (rc == 1) rc = fine_launch_rows<16, MULTI>(p, workspace, st, di.sms, false);
+    return rc;
 }
 
 }  // namespace bx
@@ -746,8 +772,8 @@ extern "C" int bx_fom_picard_finemesh_ranks(int B, int N, int node_offset, int N
     BX_REQUIRE(kmax >= 1, "kmax must be >= 1 (the reference loop body defines U1)");
     BX_REQUIRE(R >= 1 && R <= FRMAX && rank >= 0 && rank < R, "1 <= R <= %d ranks, 0 <= rank < R (got R = %d, rank = %d)", FRMAX, R, rank);
     BX_REQUIRE(N_local >= 1 && node_offset >= 0 && (long long)node_offset + N_local <= N, "node block [%d, %d + %d) outside the mesh", node_offset, node_offset, N_local);
-    BX_REQUIRE(node_offset % FNODES == 0, "node_offset must be a multiple of %d", FNODES);
-    BX_REQUIRE(node_offset + N_local == N || N_local % FNODES == 0, "every block but the last holds a multiple of %d nodes", FNODES);
+    BX_REQUIRE(node_offset % FBLOCK == 0, "node_offset must be a multiple of %d", FBLOCK);
+    BX_REQUIRE(node_offset + N_local == N || N_local % FBLOCK == 0, "every block but the last holds a multiple of %d nodes", FBLOCK);
     BX_REQUIRE((rank == 0) == (node_offset == 0) && (rank == R - 1) == (node_offset + N_local == N), "blocks must be in rank order and cover the mesh");
     if (B == 0) return BX_OK;
     BX_REQUIRE(X && u0_local && mu1 && mu2 && U_local && workspace && peer_bufs, "null pointer");

@@ -64,7 +64,8 @@ int         bx_device_sm_count(void);
 #define BX_TUNE_FOM_KERNEL               5  /* 0 throughput kernel, 1 latency kernel (speculative front half) */
 #define BX_TUNE_FOM_SEGMENT_STEPS        6  /* time steps per round-robin work unit of the FOM / POD-PROM / quadratic-manifold sweeps (0: whole trajectories) */
 #define BX_TUNE_QM_GROUP                 7  /* 1 .. 8 trajectories per lock-step group of the quadratic-manifold PROM */
-#define BX_TUNE_COUNT                    8
+#define BX_TUNE_FINE_ROWS                8  /* 4, 8 or 16 mesh rows per thread of the fine-mesh kernels (2048 / 4096 / 8192 nodes per CTA) */
+#define BX_TUNE_COUNT                    9
 int bx_set_tuning(int knob, int value);
 int bx_get_tuning(int knob);
 

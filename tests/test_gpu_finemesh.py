@@ -23,9 +23,16 @@ def _run(oracle, N, nsteps, mu1=4.75, mu2=0.02, E=0.0, X=None, u0=None, tol=1e-6
     return U[0].cpu().numpy().T, it[0].cpu().numpy(), Uo, ito
 
 
+@pytest.mark.parametrize("rows", [-1, 16, 8, 4])
 @pytest.mark.parametrize("N", [1025, 8192, 8193, 20000, 65536, 131072 + 7])
-def test_finemesh_vs_oracle(N, oracle):
-    U, it, Uo, ito = _run(oracle, N, 12)
+def test_finemesh_vs_oracle(N, rows, oracle):
+    """rows: mesh rows per thread of the kernel instance (BX_TUNE_FINE_ROWS; -1 = automatic)."""
+    import burgers_b200
+    burgers_b200.set_tuning("fine_rows", rows)
+    try:
+        U, it, Uo, ito = _run(oracle, N, 12)
+    finally:
+        burgers_b200.set_tuning("fine_rows", -1)
     assert np.array_equal(it, ito), (it, ito)
     assert rel_l2_per_step(U, Uo) <= TOL
 

@@ -61,8 +61,19 @@ def _run_ranks(X, At, nsteps, u0, mu1, E, mu2, R, launches=1):
             lib.bx_peer_free(ptr)
 
 
+@pytest.mark.parametrize("rows", [-1, 16, 8])
 @pytest.mark.parametrize("N,R", [(100003, 2), (100003, 3), (8192 * 5, 5), (131072 + 7, 8)])
-def test_ranks_vs_oracle_and_single_kernel(N, R, oracle):
+def test_ranks_vs_oracle_and_single_kernel(N, R, rows, oracle):
+    """rows: mesh rows per thread of the kernel instance (-1: automatic = 4 at these sizes)."""
+    import burgers_b200
+    burgers_b200.set_tuning("fine_rows", rows)
+    try:
+        _ranks_vs_oracle_and_single_kernel(N, R, oracle)
+    finally:
+        burgers_b200.set_tuning("fine_rows", -1)
+
+
+def _ranks_vs_oracle_and_single_kernel(N, R, oracle):
     import burgers_b200
     X = np.linspace(0.0, 100.0, N)
     At = 0.05 * 511.0 / (N - 1)
@@ -84,7 +95,12 @@ def test_ranks_two_groups_of_ctas_nonuniform_mesh_diffusion(oracle):
     X = np.cumsum(0.5 + rng.random(N)); X = 100.0 * (X - X[0]) / (X[-1] - X[0])
     At = 0.05 * 511.0 / (N - 1)
     u0 = 1.0 + 0.2 * np.sin(X / 7.0)
-    U, it = _run_ranks(X, At, 3, u0, 4.3, 1e-4, 0.017, 2)
+    import burgers_b200
+    burgers_b200.set_tuning("fine_rows", 16)   # 8192 nodes per CTA: 70 + 69 CTAs fit side by side on one device
+    try:
+        U, it = _run_ranks(X, At, 3, u0, 4.3, 1e-4, 0.017, 2)
+    finally:
+        burgers_b200.set_tuning("fine_rows", -1)
     Uo, ito = oracle.fom_burgers(X, At, 3, u0, 4.3, 1e-4, 0.017)
     assert np.array_equal(it, ito), (it, ito)
     assert rel_l2_per_step(U, Uo) <= TOL
