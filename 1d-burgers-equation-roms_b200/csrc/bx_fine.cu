@@ -46,9 +46,10 @@ constexpr int FRMAX = 8;          // ranks the rank-level solve covers
 // exchange buffer of a rank (peer-mapped by every other rank), byte offsets
 constexpr size_t PX_EPOCH = 0;        // u64: exchanges done on these buffers so far (kept by the kernels, the same on every rank)
 constexpr size_t PX_FAIL = 128;       // u64: non-zero once any rank gave up waiting
-constexpr size_t PX_PAYLOAD = 256;    // u64 [2 parities][2 kinds][FRMAX sources][16 words]
-constexpr int PX_WORDS = 14;          // 7 doubles as 14 words of (32-bit epoch tag << 32 | 32 data bits)
-constexpr size_t PX_BYTES = 256 + 2 * 2 * FRMAX * 16 * 8;
+constexpr size_t PX_PAYLOAD = 256;    // u64 [2 parities][FRMAX sources][32 words]
+constexpr int PX_VALUES = 11;         // a rank's row + fgr (7), norm partials (2), edge states (2)
+constexpr int PX_WORDS = 2 * PX_VALUES;   // each double as 2 words of (32-bit epoch tag << 32 | 32 data bits)
+constexpr size_t PX_BYTES = 256 + 2 * FRMAX * 32 * 8;
 constexpr unsigned long long PX_TIMEOUT_NS = 10ull * 1000ull * 1000ull * 1000ull;
 
 struct FineParams {
@@ -63,15 +64,31 @@ struct FineParams {
     int *iters;
     double *g_h6, *g_hfs;     // (FM+1) x FT per CTA, element jj at [(jj+1) * FT + tid]
     double *g_atf, *g_bn;     // FM x FT per CTA, node j at [j * FT + tid]
-    double *g_rows;           // [G][8]: al, be, gaE, rho, F, G, R, -
-    double *g_norm;           // [G][4]: sd, su, u_first, u_last
-    unsigned long long *bar;
+    unsigned long long *g_ll; // [2 parities][G][32]: a CTA's row + fgr (7), norm partials (2), edge states (2) as 22 tagged words
+    unsigned long long *bar;  // [16] = abort word of the rank (MULTI)
     // MULTI only: this rank's node block [off, off + Nloc) of the N-node mesh; u0 / U / iters are the block's
     int R, rank, off, Nloc;
     char *peer[FRMAX];        // exchange buffer of every rank as mapped here ([rank] = own)
 };
 
 struct Lvl { double y, z1, z2; };
+
+// BX_FINE_TRACE (experiments, tools/fine_trace.py): cycles of thread 0 of CTA 0 between marks, summed per mark
+#ifdef BX_FINE_TRACE
+__device__ unsigned long long g_fine_trace[32];
+__device__ unsigned long long g_fine_tlast;
+#define FINE_MARK(i)                                                      \
+    do {                                                                  \
+        if (threadIdx.x == 0 && blockIdx.x == 0) {                        \
+            const unsigned long long t_ = clock64();                      \
+            g_fine_trace[i] += t_ - g_fine_tlast;                         \
+            g_fine_trace[16 + (i)] += 1ull;                               \
+            g_fine_tlast = t_;                                            \
+        }                                                                 \
+    } while (0)
+#else
+#define FINE_MARK(i) do { } while (0)
+#endif
 
 __device__ __forceinline__ void warp_sum_pair(double &a, double &b) {
 #pragma unroll
@@ -134,29 +151,23 @@ __device__ __forceinline__ Lvl group_up(int m, int lane, double &al, double &be,
     return lv;
 }
 
-// all CTAs of the (co-resident, cooperative) grid; monotonic 64-bit counter, target = epoch * G (two barriers per
-// Picard iteration and G arrivals each: a 32-bit counter would wrap after a few thousand trajectories per launch).
-// MULTI: bar[16] is the rank's abort word (set when a wait on another rank timed out or a peer reported failure); a
-// CTA that sees it stops waiting and the barrier returns false — the CTA then leaves the kernel, so nothing can hang.
-template <bool MULTI>
-__device__ __forceinline__ bool grid_barrier(unsigned long long *bar, unsigned int G, unsigned long long &epoch, int *s_abort) {
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        ++epoch;
-        __threadfence();
-        atomicAdd(bar, 1ull);
-        const unsigned long long target = epoch * G;
-        unsigned long long v;
-        bool aborted = false;
-        do {
-            asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(bar) : "memory");
-            if (MULTI && *reinterpret_cast<volatile unsigned long long *>(bar + 16) != 0ull) { aborted = true; break; }
-        } while (v < target);
-        __threadfence();
-        if (MULTI) *s_abort = aborted ? 1 : 0;
-    }
-    __syncthreads();
-    return MULTI ? (*s_abort == 0) : true;
+// ---- synchronisation of the CTAs of the (co-resident, cooperative) grid without a barrier --------------------------
+// What a CTA publishes per Picard iteration — its row + fgr, the norm partials and edge states of its last update:
+// LL_VALUES doubles — travels as 2 x LL_VALUES 8-byte words of (32-bit epoch tag << 32 | 32 data bits).  An aligned
+// 8-byte store is seen whole, so a word whose tag equals the epoch IS the data: no fence, no counter, no second read;
+// every thread of every CTA polls its share of the G x 22 words (all loads of a round in flight together) and drops
+// the data halves into shared memory.  Slots alternate with the parity of the epoch: a CTA can publish epoch e + 2 only
+// after it has seen epoch e + 1 of every CTA, which they publish after all their threads have read epoch e.
+constexpr int LL_VALUES = 11;
+constexpr int LL_WORDS = 2 * LL_VALUES;
+constexpr int LL_STRIDE = 32;     // words per CTA slot (256 bytes)
+__device__ __forceinline__ void st_gpu_u64(unsigned long long *a, unsigned long long v) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(a), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_gpu_u64(const unsigned long long *a) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(a) : "memory");
+    return v;
 }
 
 // ---- peer-memory exchange between the ranks of a partitioned trajectory (MULTI) -------------------------
@@ -178,21 +189,21 @@ __device__ __forceinline__ unsigned long long ld_sys_u64(const unsigned long lon
     asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(a) : "memory");
     return v;
 }
-__device__ __forceinline__ size_t px_slot(unsigned int ep, int kind, int src) {
-    return PX_PAYLOAD + 8 * 16 * ((((size_t)(ep & 1u) * 2 + kind) * FRMAX) + src);
+__device__ __forceinline__ size_t px_slot(unsigned int ep, int src) {
+    return PX_PAYLOAD + 8 * 32 * ((size_t)(ep & 1u) * FRMAX + src);
 }
 
 // ONE warp of the rank (all 32 lanes, v identical on every lane): word w of this rank's 7 values goes to every rank's
 // buffer, one store per (destination, word) spread over the lanes
-__device__ __forceinline__ void peer_publish(const FineParams &p, int kind, unsigned int ep, int lane, const double (&v)[8]) {
+__device__ __forceinline__ void peer_publish(const FineParams &p, unsigned int ep, int lane, const double (&v)[PX_VALUES]) {
     const int total = p.R * PX_WORDS;
     for (int idx = lane; idx < total; idx += 32) {
         const int dst = idx / PX_WORDS, w = idx - dst * PX_WORDS;
         double d = v[0];
 #pragma unroll
-        for (int i = 1; i < 7; ++i) d = (w >> 1) == i ? v[i] : d;
+        for (int i = 1; i < PX_VALUES; ++i) d = (w >> 1) == i ? v[i] : d;
         const unsigned int half = (w & 1) ? (unsigned int)__double2hiint(d) : (unsigned int)__double2loint(d);
-        unsigned long long *slot = reinterpret_cast<unsigned long long *>(p.peer[dst] + px_slot(ep, kind, p.rank));
+        unsigned long long *slot = reinterpret_cast<unsigned long long *>(p.peer[dst] + px_slot(ep, p.rank));
         st_sys_u64(slot + w, ((unsigned long long)ep << 32) | half);
     }
 }
@@ -201,12 +212,12 @@ __device__ __forceinline__ void peer_publish(const FineParams &p, int kind, unsi
 // 7 values (v[7] = 0; lanes >= R: zeros).  A wait that exceeds PX_TIMEOUT_NS, or a failure word set by anybody, raises the
 // failure word of every rank and this rank's abort word; the values are then meaningless and the next grid barrier
 // ends the kernel.
-__device__ __forceinline__ void peer_gather(const FineParams &p, int kind, unsigned int ep, int lane, double (&v)[8]) {
+__device__ __forceinline__ void peer_gather(const FineParams &p, unsigned int ep, int lane, double (&v)[PX_VALUES]) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) v[i] = 0.0;
+    for (int i = 0; i < PX_VALUES; ++i) v[i] = 0.0;
     if (lane < p.R) {
         char *own = p.peer[p.rank];
-        const unsigned long long *slot = reinterpret_cast<const unsigned long long *>(own + px_slot(ep, kind, lane));
+        const unsigned long long *slot = reinterpret_cast<const unsigned long long *>(own + px_slot(ep, lane));
         volatile unsigned long long *failw = reinterpret_cast<volatile unsigned long long *>(own + PX_FAIL);
         volatile unsigned long long *abortw = reinterpret_cast<volatile unsigned long long *>(p.bar + 16);
         unsigned long long t0 = 0ull;
@@ -233,7 +244,7 @@ __device__ __forceinline__ void peer_gather(const FineParams &p, int kind, unsig
             __threadfence_system();
         } else {
 #pragma unroll
-            for (int i = 0; i < 7; ++i) v[i] = __hiloint2double((int)(unsigned int)wd[2 * i + 1], (int)(unsigned int)wd[2 * i]);
+            for (int i = 0; i < PX_VALUES; ++i) v[i] = __hiloint2double((int)(unsigned int)wd[2 * i + 1], (int)(unsigned int)wd[2 * i]);
         }
     }
     __syncwarp();
@@ -250,10 +261,12 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
     double *s_top = s_x + 8 * FW;           // [FGMAX + 1]: x_last of CTA c at [c + 1], [0] = 0
     double *s_wx = s_top + FGMAX + 2;       // [FW + 1]: x_last of warp w at [w + 1], [0] = CTA's P
     double *s_red = s_wx + FW + 2;          // [FW][4] norm partials / warp edge states
-    double *s_dec = s_red + 4 * FW;         // [4]: sd, su, uL of the CTA, uR of the CTA
-    double *s_grp = s_dec + 4;              // MULTI: [5][8] rows + fgr of the groups of 32 CTAs
+    double *s_dec = s_red + 4 * FW;         // [10]: sd, su | states outside the CTA: corrected L, R, current L, R | rank: L, R, dR
+    double *s_grp = s_dec + 10;             // MULTI: [5][8] rows + fgr of the groups of 32 CTAs
     double *s_gx = s_grp + 40;              // MULTI: [6]: x_last of group g at [g + 1], [0] = the rank's P
     int *s_abort = reinterpret_cast<int *>(s_gx + 8);
+    double *s_rows = s_x + 512;             // [G][LL_VALUES]: what every CTA published for this synchronisation
+    unsigned int *s_rows32 = reinterpret_cast<unsigned int *>(s_rows);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int cta = blockIdx.x, G = p.G, N = p.N;
@@ -265,14 +278,10 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
     const double a6 = At / 6.0, c1 = 1.5 * At;
     const bool has_e = p.E != 0.0;
     const double ate = At * p.E;
-    unsigned long long epoch = 0;
-    // epochs of the two kinds of exchange between ranks: they continue where the last launch on these buffers stopped
-    unsigned int xe0 = 0u, xe1 = 0u;
-    if (MULTI) {
-        const volatile unsigned long long *ew = reinterpret_cast<const volatile unsigned long long *>(p.peer[p.rank] + PX_EPOCH);
-        xe0 = (unsigned int)ew[0];
-        xe1 = (unsigned int)ew[1];
-    }
+    unsigned int nsync = 0u;   // synchronisations so far = epoch of the last one
+    // epoch of the exchanges between ranks: continues where the last launch on these buffers stopped
+    unsigned int xe = 0u;
+    if (MULTI) xe = (unsigned int)*reinterpret_cast<const volatile unsigned long long *>(p.peer[p.rank] + PX_EPOCH);
 
     double *t_h6 = p.g_h6 + (size_t)cta * (FM + 1) * FT + tid;
     double *t_hfs = p.g_hfs + (size_t)cta * (FM + 1) * FT + tid;
@@ -288,6 +297,7 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
         t_h6[(jj + 1) * FT] = h6;
     }
 
+    if (MULTI && tid == 0) *s_abort = 0;
     const bool leftv = node0 > 0 && jl >= 0;
     const double a6L = leftv ? a6 : 0.0, c1L = leftv ? c1 : 0.0;
 
@@ -325,62 +335,221 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
             }
         }
         double sd = 0.0, su = 0.0, uL = 0.0, uR = 0.0;
+        double m_pa = 0.0, m_pb = 0.0, m_eF = 0.0, m_eL = 0.0;   // warp 0: norm partials of the CTA's last update, its edge states
 
-        // publish partition-edge states (and norm partials), grid barrier, fetch neighbours' edges and
-        // the grid-wide norms (summed in CTA order)
-        auto exchange = [&](double psd, double psu) -> bool {
+        // After an update, inside the CTA: the neighbours' edge states through shuffles / shared memory, the CTA's norm
+        // partials and own edge states into warp 0 (they travel with the next rows); the states just outside the CTA are
+        // s_dec[slotL], s_dec[slotR]
+        auto cta_edges = [&](double psd, double psu, int slotL, int slotR) {
             warp_sum_pair(psd, psu);
             if (lane == 0) { s_red[4 * warp + 0] = psd; s_red[4 * warp + 1] = psu; s_red[4 * warp + 2] = u[0]; }
             if (lane == 31) s_red[4 * warp + 3] = u[FM - 1];
             __syncthreads();
-            if (tid == 0) {
+            if (warp == 0) {
                 double a = 0.0, b = 0.0;
                 for (int w = 0; w < FW; ++w) { a += s_red[4 * w]; b += s_red[4 * w + 1]; }
-                double *gn = p.g_norm + 4 * cta;
-                gn[0] = a; gn[1] = b; gn[2] = s_red[2]; gn[3] = s_red[4 * (FW - 1) + 3];
+                m_pa = a; m_pb = b; m_eF = s_red[2]; m_eL = s_red[4 * (FW - 1) + 3];
             }
-            if (!grid_barrier<MULTI>(p.bar, (unsigned)G, epoch, s_abort)) return false;
-            if (warp == 0) {
-                // sum of G partials, fixed order: lane l takes CTAs 5 l .. 5 l + 4, then a butterfly
-                double a = 0.0, b = 0.0;
-                for (int c = 5 * lane; c < 5 * lane + 5 && c < G; ++c) {
-                    a += __ldcg(p.g_norm + 4 * c); b += __ldcg(p.g_norm + 4 * c + 1);
-                }
-                warp_sum_pair(a, b);
-                double eL = 0.0, eR = 0.0;   // states just outside the rank's block
-                if (MULTI) {
-                    // the rank's partials and edge states go to every rank; the sums run in rank order
-                    ++xe1;
-                    double v[8];
-                    if (cta == 0) {
-                        v[0] = a; v[1] = b; v[2] = __ldcg(p.g_norm + 2); v[3] = __ldcg(p.g_norm + 4 * (G - 1) + 3);
-                        v[4] = v[5] = v[6] = v[7] = 0.0;
-                        peer_publish(p, 1, xe1, lane, v);
-                    }
-                    peer_gather(p, 1, xe1, lane, v);
-                    a = 0.0; b = 0.0;
-                    for (int r = 0; r < p.R; ++r) { a += shfl_idx(v[0], r); b += shfl_idx(v[1], r); }
-                    eL = shfl_idx(v[3], p.rank > 0 ? p.rank - 1 : 0);
-                    eR = shfl_idx(v[2], p.rank < p.R - 1 ? p.rank + 1 : p.rank);
-                    if (p.rank == 0) eL = 0.0;
-                    if (p.rank == p.R - 1) eR = 0.0;
-                }
-                if (lane == 0) {
-                    s_dec[0] = a; s_dec[1] = b;
-                    s_dec[2] = cta > 0 ? __ldcg(p.g_norm + 4 * (cta - 1) + 3) : eL;
-                    s_dec[3] = cta < G - 1 ? __ldcg(p.g_norm + 4 * (cta + 1) + 2) : eR;
-                }
-            }
-            __syncthreads();
-            sd = s_dec[0]; su = s_dec[1];
             uL = shfl_up(u[FM - 1], 1);
             uR = shfl_down(u[0], 1);
-            if (lane == 0) uL = warp > 0 ? s_red[4 * (warp - 1) + 3] : s_dec[2];
-            if (lane == 31) uR = warp < FW - 1 ? s_red[4 * (warp + 1) + 2] : s_dec[3];
-            __syncthreads();   // s_red / s_dec are rewritten by the next exchange
+            if (lane == 0) uL = warp > 0 ? s_red[4 * (warp - 1) + 3] : s_dec[slotL];
+            if (lane == 31) uR = warp < FW - 1 ? s_red[4 * (warp + 1) + 2] : s_dec[slotR];
+        };
+
+        // ONE synchronisation of the whole mesh per Picard iteration.  In: the CTA's row + fgr (warp 0) and lc.  They are
+        // published together with the norm partials and edge states of the PREVIOUS update (double-buffered by the parity
+        // of the synchronisation: a CTA can run at most one synchronisation ahead of another).  Out: sd, su of the
+        // previous update (summed in CTA order, then rank order: every CTA takes the same decision), x_last of every warp
+        // of this CTA in s_wx, and the states just outside the CTA: s_dec[4], s_dec[5] as the neighbours hold them now,
+        // s_dec[2], s_dec[3] with this solve's correction added (x_last of the CTA before, x_first of the CTA after —
+        // what the neighbours will hold after applying this solve).
+        auto sync_step = [&](double a2, double b2, double g2, double r2, double F2, double G2, double R2, const Lvl &lc) -> bool {
+            const unsigned int ep = ++nsync;   // tags start at 1: the buffer is zeroed at launch
+            unsigned long long *slots = p.g_ll + (size_t)(ep & 1u) * ((size_t)G * LL_STRIDE);
+            if (warp == 0 && lane < LL_WORDS) {
+                const int vi = lane >> 1;
+                double d = a2;
+                d = vi == 1 ? b2 : d; d = vi == 2 ? g2 : d; d = vi == 3 ? r2 : d; d = vi == 4 ? F2 : d; d = vi == 5 ? G2 : d;
+                d = vi == 6 ? R2 : d; d = vi == 7 ? m_pa : d; d = vi == 8 ? m_pb : d; d = vi == 9 ? m_eF : d; d = vi == 10 ? m_eL : d;
+                const unsigned int half = (lane & 1) ? (unsigned int)__double2hiint(d) : (unsigned int)__double2loint(d);
+                st_gpu_u64(slots + (size_t)cta * LL_STRIDE + lane, ((unsigned long long)ep << 32) | half);
+            }
+            FINE_MARK(4);
+            {
+                // word idx = 22 c + w of the G x 22 goes to thread idx mod FT; its data half lands at s_rows32[idx]
+                constexpr int MAXW = (FGMAX * LL_WORDS + FT - 1) / FT;
+                const int total = G * LL_WORDS;
+                volatile unsigned long long *abortw = reinterpret_cast<volatile unsigned long long *>(p.bar + 16);
+                unsigned long long wd[MAXW];
+                unsigned spins = 0;
+                for (;;) {
+                    bool all = true;
+#pragma unroll
+                    for (int q = 0; q < MAXW; ++q) {
+                        const int idx = tid + q * FT;
+                        if (idx < total) {
+                            const int c = idx / LL_WORDS;
+                            wd[q] = ld_gpu_u64(slots + (size_t)c * LL_STRIDE + (idx - c * LL_WORDS));
+                        }
+                    }
+#pragma unroll
+                    for (int q = 0; q < MAXW; ++q)
+                        if (tid + q * FT < total) all = all && (unsigned int)(wd[q] >> 32) == ep;
+                    if (all) break;
+                    if (MULTI && (++spins & 255u) == 0u && *abortw != 0ull) { *s_abort = 1; break; }
+                }
+#pragma unroll
+                for (int q = 0; q < MAXW; ++q)
+                    if (tid + q * FT < total) s_rows32[tid + q * FT] = (unsigned int)wd[q];
+            }
+            FINE_MARK(5);
+            __syncthreads();
+            FINE_MARK(6);
+            if (MULTI && *s_abort != 0) return false;
+            if (MULTI) {
+                // ---- rank level: fold the G rows of this rank, exchange with the other ranks, unfold --------------
+                const int ng = (G + 31) >> 5;   // groups of 32 CTAs, one per warp
+                Lvl l1; l1.y = 0.0; l1.z1 = 0.0; l1.z2 = 0.0;
+                if (warp < ng) {
+                    const int c = 32 * warp + lane;
+                    double a3 = 0.0, b3 = 1.0, g3 = 0.0, r3 = 0.0, F3 = 0.0, G3 = 0.0, R3 = 0.0;
+                    if (c < G) {
+                        const double *d = s_rows + LL_VALUES * c;
+                        a3 = d[0]; b3 = d[1]; g3 = d[2]; r3 = d[3]; F3 = d[4]; G3 = d[5]; R3 = d[6];
+                    }
+                    const int m = G - 32 * warp < 32 ? G - 32 * warp : 32;
+                    l1 = group_up(m, lane, a3, b3, g3, r3, F3, G3, R3);
+                    if (lane == 0) {
+                        double *d = s_grp + 8 * warp;
+                        d[0] = a3; d[1] = b3; d[2] = g3; d[3] = r3; d[4] = F3; d[5] = G3; d[6] = R3;
+                    }
+                }
+                __syncthreads();
+                if (warp == 0) {
+                    double a4 = 0.0, b4 = 1.0, g4 = 0.0, r4 = 0.0, F4 = 0.0, G4 = 0.0, R4 = 0.0;
+                    if (lane < ng) {
+                        const double *d = s_grp + 8 * lane;
+                        a4 = d[0]; b4 = d[1]; g4 = d[2]; r4 = d[3]; F4 = d[4]; G4 = d[5]; R4 = d[6];
+                    }
+                    const Lvl l2 = group_up(ng, lane, a4, b4, g4, r4, F4, G4, R4);   // -> the rank's row + fgr
+                    // the rank's norm partials, fixed order: lane l takes CTAs 5 l .. 5 l + 4, then a butterfly
+                    double ra = 0.0, rb = 0.0;
+                    for (int c = 5 * lane; c < 5 * lane + 5 && c < G; ++c) { ra += s_rows[LL_VALUES * c + 7]; rb += s_rows[LL_VALUES * c + 8]; }
+                    warp_sum_pair(ra, rb);
+                    ++xe;
+                    double v[PX_VALUES];
+                    if (cta == 0) {
+                        v[0] = a4; v[1] = b4; v[2] = g4; v[3] = r4; v[4] = F4; v[5] = G4; v[6] = R4;
+                        v[7] = ra; v[8] = rb; v[9] = s_rows[9]; v[10] = s_rows[LL_VALUES * (G - 1) + 10];
+                        peer_publish(p, xe, lane, v);
+                    }
+                    peer_gather(p, xe, lane, v);
+                    double a = 0.0, b = 0.0;
+                    for (int r = 0; r < p.R; ++r) { a += shfl_idx(v[7], r); b += shfl_idx(v[8], r); }
+                    // closed R-row system: one more group_up (lanes >= R hold identity rows), then the group's row
+                    // with nothing left (P = 0) or right (ga = 0) of the mesh gives x_last of the last rank
+                    double a5 = 0.0, b5 = 1.0, g5 = 0.0, r5 = 0.0, F5 = 0.0, G5 = 0.0, R5 = 0.0;
+                    if (lane < p.R) { a5 = v[0]; b5 = v[1]; g5 = v[2]; r5 = v[3]; F5 = v[4]; G5 = v[5]; R5 = v[6]; }
+                    const Lvl l3 = group_up(p.R, lane, a5, b5, g5, r5, F5, G5, R5);
+                    const double Xtop = r5 * rcp(b5);
+                    const double xr = fma(Xtop, l3.z2, l3.y);          // x_last of rank `lane`
+                    double Pr = shfl_idx(xr, p.rank > 0 ? p.rank - 1 : 0);
+                    if (p.rank == 0) Pr = 0.0;
+                    const double Xr = shfl_idx(xr, p.rank);
+                    // states just outside the rank's block, and the correction of the one on the right: x_first of the next rank
+                    const int rn = p.rank < p.R - 1 ? p.rank + 1 : p.rank;
+                    double tLr = shfl_idx(v[10], p.rank > 0 ? p.rank - 1 : 0), tRr = shfl_idx(v[9], rn);
+                    double dRr = fma(-shfl_idx(v[5], rn), shfl_idx(xr, rn), fma(-shfl_idx(v[4], rn), Xr, shfl_idx(v[6], rn)));
+                    if (p.rank == 0) tLr = 0.0;
+                    if (p.rank == p.R - 1) { tRr = 0.0; dRr = 0.0; }
+                    if (lane < ng) s_gx[lane + 1] = fma(Xr, l2.z2, fma(-Pr, l2.z1, l2.y));
+                    if (lane == 0) {
+                        s_gx[0] = Pr;
+                        s_dec[0] = a; s_dec[1] = b; s_dec[6] = tLr; s_dec[7] = tRr; s_dec[8] = dRr;
+                    }
+                }
+                __syncthreads();
+                if (warp < ng) {
+                    const double Pg = s_gx[warp], Xg = s_gx[warp + 1];
+                    if (32 * warp + lane < G) s_top[32 * warp + lane + 1] = fma(Xg, l1.z2, fma(-Pg, l1.z1, l1.y));
+                    if (warp == 0 && lane == 0) s_top[0] = Pg;
+                }
+                __syncthreads();
+            }
+            if (!MULTI && warp == 0) {   // ---- grid level: closed G-row system, solved by every CTA
+                constexpr int TM = FGMAX / 32;   // 5 rows per lane
+                double cs5[TM], rs5[TM], fs5[TM];
+                Continuant<TM> ct;
+#pragma unroll
+                for (int j = 0; j < TM; ++j) {
+                    const int c = lane * TM + j;
+                    double a = 0.0, b = 1.0, cc = 0.0, r = 0.0;
+                    if (c < G) {
+                        const double *d = s_rows + LL_VALUES * c;
+                        a = d[0]; b = d[1]; r = d[3];
+                        if (c < G - 1) {   // E of CTA c = x_first of CTA c+1
+                            const double gE = d[2];
+                            const double Fn = d[LL_VALUES + 4], Gn = d[LL_VALUES + 5], Rn = d[LL_VALUES + 6];
+                            b = fma(-gE, Fn, b); cc = -gE * Gn; r = fma(-gE, Rn, r);
+                        }
+                        if (c == 0) a = 0.0;
+                    }
+                    ct.row(j, a, b, cc, r, cs5[j], rs5[j], fs5[j]);
+                }
+                double xl, P;
+                partition_condense<TM>(cs5, rs5, fs5, lane, xl, P);
+                double x = xl;
+#pragma unroll
+                for (int j = TM - 1; j >= 0; --j) {
+                    if (j < TM - 1) x = fma(-cs5[j], x, fma(-fs5[j], P, rs5[j]));
+                    s_top[lane * TM + j + 1] = x;
+                }
+                if (lane == 0) s_top[0] = 0.0;
+                __syncwarp();
+                FINE_MARK(8);
+
+                // norms of the previous update, fixed order: lane l takes CTAs 5 l .. 5 l + 4, then a butterfly
+                double a = 0.0, b = 0.0;
+                for (int c = 5 * lane; c < 5 * lane + 5 && c < G; ++c) { a += s_rows[LL_VALUES * c + 7]; b += s_rows[LL_VALUES * c + 8]; }
+                warp_sum_pair(a, b);
+                if (lane == 0) { s_dec[0] = a; s_dec[1] = b; s_dec[6] = 0.0; s_dec[7] = 0.0; s_dec[8] = 0.0; }
+                __syncwarp();
+            }
+            if (warp == 0) {
+                // CTA level, downwards: x_last of every warp; the states just outside the CTA
+                const double Pc = s_top[cta], Xc = s_top[cta + 1];
+                if (lane < FW) s_wx[lane + 1] = fma(Xc, lc.z2, fma(-Pc, lc.z1, lc.y));
+                if (lane == 0) {
+                    s_wx[0] = Pc;
+                    const double tL = cta > 0 ? s_rows[LL_VALUES * (cta - 1) + 10] : s_dec[6];
+                    double tR = s_dec[7], dR = s_dec[8];
+                    if (cta < G - 1) {   // x_first of the next CTA = R - F x_last(this CTA) - G x_last(next CTA)
+                        const double *d = s_rows + LL_VALUES * (cta + 1);
+                        tR = d[9];
+                        dR = fma(-d[5], s_top[cta + 2], fma(-d[4], Xc, d[6]));
+                    }
+                    s_dec[2] = tL + Pc; s_dec[3] = tR + dR; s_dec[4] = tL; s_dec[5] = tR;
+                }
+            }
+            FINE_MARK(9);
+            __syncthreads();
+            FINE_MARK(10);
+            sd = s_dec[0]; su = s_dec[1];
             return true;
         };
-        if (!exchange(0.0, 0.0)) return;
+        // the states just outside the CTA as the neighbours hold them (sample start; after a discarded front half)
+        auto adopt_edges = [&]() {
+            if (tid == 0) uL = s_dec[4];
+            if (tid == FT - 1) uR = s_dec[5];
+        };
+
+        // sample start: one synchronisation with identity rows brings the neighbours' edge states
+        cta_edges(0.0, 0.0, 4, 5);
+        {
+            Lvl li; li.y = 0.0; li.z1 = 0.0; li.z2 = 0.0;
+            if (!sync_step(0.0, 1.0, 0.0, 0.0, 0.0, 0.0, 0.0, li)) return;
+            adopt_edges();
+        }
 
         for (int n = 0; n < p.nsteps; ++n) {
             // ---- bn = M U^n + At F (constant during the Picard loop, :683) ---------------------
@@ -395,8 +564,13 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
                     h6L = h6R;
                 }
             }
+            // Picard loop (:663-698) with the convergence test one synchronisation late: the norms of update k travel with the
+            // rows of iteration k + 1, whose front half (assembly, sweeps, condensation) is therefore speculative — it is
+            // discarded when update k turns out to have converged (or reached kmax).  u is only ever changed by confirmed
+            // iterations, so states and counts are those of the reference loop.
             int k = 0;
-            do {
+            FINE_MARK(13);
+            for (;;) {
                 // ================= thread level: assemble + sweep (:667-692) ======================
                 double al, be, ga, rho, F, Gc, R;
                 {
@@ -451,124 +625,28 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
                     }
                 }
                 // ================= warp level ====================================================
+                FINE_MARK(0);
                 const Lvl lw = group_up(32, lane, al, be, ga, rho, F, Gc, R);
                 if (lane == 0) {
                     double *d = s_wrow + 8 * warp;
                     d[0] = al; d[1] = be; d[2] = ga; d[3] = rho; d[4] = F; d[5] = Gc; d[6] = R;
                 }
+                FINE_MARK(1);
                 __syncthreads();
-                // ================= CTA level (warp 0) + publish ==================================
+                FINE_MARK(2);
+                // ================= CTA level (warp 0) ==============================================
                 Lvl lc; lc.y = 0.0; lc.z1 = 0.0; lc.z2 = 0.0;
+                double a2 = 0.0, b2 = 1.0, g2 = 0.0, r2 = 0.0, F2 = 0.0, G2 = 0.0, R2 = 0.0;
                 if (warp == 0) {
-                    double a2 = 0.0, b2 = 1.0, g2 = 0.0, r2 = 0.0, F2 = 0.0, G2 = 0.0, R2 = 0.0;
                     if (lane < FW) {
                         const double *d = s_wrow + 8 * lane;
                         a2 = d[0]; b2 = d[1]; g2 = d[2]; r2 = d[3]; F2 = d[4]; G2 = d[5]; R2 = d[6];
                     }
                     lc = group_up(FW, lane, a2, b2, g2, r2, F2, G2, R2);
-                    if (lane == 0) {
-                        double *d = p.g_rows + 8 * cta;
-                        d[0] = a2; d[1] = b2; d[2] = g2; d[3] = r2; d[4] = F2; d[5] = G2; d[6] = R2;
-                    }
                 }
-                if (!grid_barrier<MULTI>(p.bar, (unsigned)G, epoch, s_abort)) return;
-                if (MULTI) {
-                    // ================= rank level: fold the G rows of this rank, exchange, unfold ===========
-                    const int ng = (G + 31) >> 5;   // groups of 32 CTAs, one per warp
-                    Lvl l1; l1.y = 0.0; l1.z1 = 0.0; l1.z2 = 0.0;
-                    if (warp < ng) {
-                        const int c = 32 * warp + lane;
-                        double a3 = 0.0, b3 = 1.0, g3 = 0.0, r3 = 0.0, F3 = 0.0, G3 = 0.0, R3 = 0.0;
-                        if (c < G) {
-                            const double *d = p.g_rows + 8 * c;
-                            a3 = __ldcg(d); b3 = __ldcg(d + 1); g3 = __ldcg(d + 2); r3 = __ldcg(d + 3);
-                            F3 = __ldcg(d + 4); G3 = __ldcg(d + 5); R3 = __ldcg(d + 6);
-                        }
-                        const int m = G - 32 * warp < 32 ? G - 32 * warp : 32;
-                        l1 = group_up(m, lane, a3, b3, g3, r3, F3, G3, R3);
-                        if (lane == 0) {
-                            double *d = s_grp + 8 * warp;
-                            d[0] = a3; d[1] = b3; d[2] = g3; d[3] = r3; d[4] = F3; d[5] = G3; d[6] = R3;
-                        }
-                    }
-                    __syncthreads();
-                    if (warp == 0) {
-                        double a4 = 0.0, b4 = 1.0, g4 = 0.0, r4 = 0.0, F4 = 0.0, G4 = 0.0, R4 = 0.0;
-                        if (lane < ng) {
-                            const double *d = s_grp + 8 * lane;
-                            a4 = d[0]; b4 = d[1]; g4 = d[2]; r4 = d[3]; F4 = d[4]; G4 = d[5]; R4 = d[6];
-                        }
-                        const Lvl l2 = group_up(ng, lane, a4, b4, g4, r4, F4, G4, R4);   // -> the rank's row + fgr
-                        ++xe0;
-                        double v[8];
-                        if (cta == 0) {
-                            v[0] = a4; v[1] = b4; v[2] = g4; v[3] = r4; v[4] = F4; v[5] = G4; v[6] = R4; v[7] = 0.0;
-                            peer_publish(p, 0, xe0, lane, v);
-                        }
-                        peer_gather(p, 0, xe0, lane, v);
-                        // closed R-row system: one more group_up (lanes >= R hold identity rows), then the group's row
-                        // with nothing left (P = 0) or right (ga = 0) of the mesh gives x_last of the last rank
-                        double a5 = 0.0, b5 = 1.0, g5 = 0.0, r5 = 0.0, F5 = 0.0, G5 = 0.0, R5 = 0.0;
-                        if (lane < p.R) { a5 = v[0]; b5 = v[1]; g5 = v[2]; r5 = v[3]; F5 = v[4]; G5 = v[5]; R5 = v[6]; }
-                        const Lvl l3 = group_up(p.R, lane, a5, b5, g5, r5, F5, G5, R5);
-                        const double Xtop = r5 * rcp(b5);
-                        const double xr = fma(Xtop, l3.z2, l3.y);          // x_last of rank `lane`
-                        double Pr = shfl_idx(xr, p.rank > 0 ? p.rank - 1 : 0);
-                        if (p.rank == 0) Pr = 0.0;
-                        const double Xr = shfl_idx(xr, p.rank);
-                        if (lane < ng) s_gx[lane + 1] = fma(Xr, l2.z2, fma(-Pr, l2.z1, l2.y));
-                        if (lane == 0) s_gx[0] = Pr;
-                    }
-                    __syncthreads();
-                    if (warp < ng) {
-                        const double Pg = s_gx[warp], Xg = s_gx[warp + 1];
-                        if (32 * warp + lane < G) s_top[32 * warp + lane + 1] = fma(Xg, l1.z2, fma(-Pg, l1.z1, l1.y));
-                        if (warp == 0 && lane == 0) s_top[0] = Pg;
-                    }
-                    __syncthreads();
-                    if (warp == 0) {
-                        const double Pc = s_top[cta], Xc = s_top[cta + 1];
-                        if (lane < FW) s_wx[lane + 1] = fma(Xc, lc.z2, fma(-Pc, lc.z1, lc.y));
-                        if (lane == 0) s_wx[0] = Pc;
-                    }
-                }
-                // ================= grid level: closed G-row system, solved by every CTA ===========
-                if (!MULTI && warp == 0) {
-                    constexpr int TM = FGMAX / 32;   // 5 rows per lane
-                    double cs5[TM], rs5[TM], fs5[TM];
-                    Continuant<TM> ct;
-#pragma unroll
-                    for (int j = 0; j < TM; ++j) {
-                        const int c = lane * TM + j;
-                        double a = 0.0, b = 1.0, cc = 0.0, r = 0.0;
-                        if (c < G) {
-                            const double *d = p.g_rows + 8 * c;
-                            a = __ldcg(d); b = __ldcg(d + 1); r = __ldcg(d + 3);
-                            if (c < G - 1) {   // E of CTA c = x_first of CTA c+1
-                                const double gE = __ldcg(d + 2);
-                                const double Fn = __ldcg(d + 8 + 4), Gn = __ldcg(d + 8 + 5), Rn = __ldcg(d + 8 + 6);
-                                b = fma(-gE, Fn, b); cc = -gE * Gn; r = fma(-gE, Rn, r);
-                            }
-                            if (c == 0) a = 0.0;
-                        }
-                        ct.row(j, a, b, cc, r, cs5[j], rs5[j], fs5[j]);
-                    }
-                    double xl, P;
-                    partition_condense<TM>(cs5, rs5, fs5, lane, xl, P);
-                    double x = xl;
-#pragma unroll
-                    for (int j = TM - 1; j >= 0; --j) {
-                        if (j < TM - 1) x = fma(-cs5[j], x, fma(-fs5[j], P, rs5[j]));
-                        s_top[lane * TM + j + 1] = x;
-                    }
-                    if (lane == 0) s_top[0] = 0.0;
-                    __syncwarp();
-                    // CTA level, downwards: x_last of every warp
-                    const double Pc = s_top[cta], Xc = s_top[cta + 1];
-                    if (lane < FW) s_wx[lane + 1] = fma(Xc, lc.z2, fma(-Pc, lc.z1, lc.y));
-                    if (lane == 0) s_wx[0] = Pc;
-                }
-                __syncthreads();
+                FINE_MARK(3);
+                if (!sync_step(a2, b2, g2, r2, F2, G2, R2, lc)) return;
+                if (k > 0 && !(sd > p.tol2 * su && k < p.kmax)) { adopt_edges(); break; }
                 // ================= warp level, downwards; back-substitution, update, norms ========
                 double psd = 0.0, psu = 0.0;
                 {
@@ -585,9 +663,11 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
                         psu = fma(u[j], u[j], psu);
                     }
                 }
-                if (!exchange(psd, psu)) return;
+                FINE_MARK(11);
+                cta_edges(psd, psu, 2, 3);
+                FINE_MARK(12);
                 ++k;
-            } while (sd > p.tol2 * su && k < p.kmax);
+            }
 
             // ---- snapshot n+1 (:705) and iteration count -------------------------------------------
             double *Un1 = Us + (long long)(n + 1) * Nl + (node0 - off);
@@ -604,17 +684,15 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
                 p.iters[(long long)smp * p.nsteps + n] = (su <= 1.7976931348623157e308) ? k : -1;
         }
     }
-    if (MULTI && cta == 0 && tid == 0) {   // the next launch on these buffers continues the epochs
-        volatile unsigned long long *ew = reinterpret_cast<volatile unsigned long long *>(p.peer[p.rank] + PX_EPOCH);
-        ew[0] = xe0; ew[1] = xe1;
-    }
+    if (MULTI && cta == 0 && tid == 0)   // the next launch on these buffers continues the epochs
+        *reinterpret_cast<volatile unsigned long long *>(p.peer[p.rank] + PX_EPOCH) = xe;
 }
 
-constexpr size_t fine_smem(int fm) { return sizeof(double) * (3 * (size_t)fm * FT + 512); }
+constexpr size_t fine_smem(int fm) { return sizeof(double) * (3 * (size_t)fm * FT + 512 + (size_t)FGMAX * LL_VALUES); }
 
 struct FinePlan {
     int G;
-    size_t off_h6, off_hfs, off_atf, off_bn, off_rows, off_norm, total;
+    size_t off_h6, off_hfs, off_atf, off_bn, off_ll, ll_bytes, total;
 };
 
 static int fine_plan(int N, int fm, FinePlan &pl) {
@@ -626,8 +704,8 @@ static int fine_plan(int N, int fm, FinePlan &pl) {
     pl.off_hfs = take((size_t)pl.G * (fm + 1) * FT);
     pl.off_atf = take((size_t)pl.G * nodes);
     pl.off_bn = take((size_t)pl.G * nodes);
-    pl.off_rows = take((size_t)(pl.G + 1) * 8);
-    pl.off_norm = take((size_t)pl.G * 4);
+    pl.off_ll = take(2 * (size_t)pl.G * LL_STRIDE);   // double-buffered by the parity of the synchronisation
+    pl.ll_bytes = sizeof(unsigned long long) * 2 * (size_t)pl.G * LL_STRIDE;
     pl.total = o;
     return BX_OK;
 }
@@ -672,9 +750,9 @@ static int fine_launch_rows(FineParams &p, void *workspace, cudaStream_t st, int
     p.g_hfs = reinterpret_cast<double *>(ws + pl.off_hfs);
     p.g_atf = reinterpret_cast<double *>(ws + pl.off_atf);
     p.g_bn = reinterpret_cast<double *>(ws + pl.off_bn);
-    p.g_rows = reinterpret_cast<double *>(ws + pl.off_rows);
-    p.g_norm = reinterpret_cast<double *>(ws + pl.off_norm);
+    p.g_ll = reinterpret_cast<unsigned long long *>(ws + pl.off_ll);
     BX_CUDA(cudaMemsetAsync(p.bar, 0, 256, st));
+    BX_CUDA(cudaMemsetAsync(p.g_ll, 0, pl.ll_bytes, st));
     void *args[] = {&p};
     BX_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void *>(fine_fom_kernel<FM, MULTI>), dim3(pl.G), dim3(FT), args,
                                         fine_smem(FM), st));
@@ -801,3 +879,16 @@ extern "C" int bx_fine_peer_failed(const void *own_buf, void *stream) {
     BX_CUDA(cudaStreamSynchronize(st));
     return w != 0ull ? 1 : 0;
 }
+
+#ifdef BX_FINE_TRACE
+extern "C" int bx_fine_trace_read(unsigned long long *out32, int reset) {
+    using namespace bx;
+    BX_CUDA(cudaDeviceSynchronize());
+    BX_CUDA(cudaMemcpyFromSymbol(out32, g_fine_trace, sizeof(unsigned long long) * 32));
+    if (reset) {
+        unsigned long long z[32] = {};
+        BX_CUDA(cudaMemcpyToSymbol(g_fine_trace, z, sizeof z));
+    }
+    return BX_OK;
+}
+#endif
