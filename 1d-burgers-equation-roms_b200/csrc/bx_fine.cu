@@ -62,8 +62,7 @@ struct FineParams {
     double At, E, tol2;
     double *U;
     int *iters;
-    double *g_h6, *g_hfs;     // (FM+1) x FT per CTA, element jj at [(jj+1) * FT + tid]
-    double *g_atf, *g_bn;     // FM x FT per CTA, node j at [j * FT + tid]
+    double *g_thr;            // per CTA: h6 | hfs ((FM+1) x FT each, element jj at [(jj+1) * FT + tid]) | atf | bn (FM x FT each, node j at [j * FT + tid])
     unsigned long long *g_ll; // [2 parities][G][32]: a CTA's row + fgr (7), norm partials (2), edge states (2) as 22 tagged words
     unsigned long long *bar;  // [16] = abort word of the rank (MULTI)
     // MULTI only: this rank's node block [off, off + Nloc) of the N-node mesh; u0 / U / iters are the block's
@@ -113,6 +112,8 @@ __device__ __forceinline__ void pcr_step3(double &al, double &be, double &ga, do
 // Group m (<= 32) consecutive partitions, one per lane (lanes >= m must hold identity rows:
 // al = ga = 0, be = 1, rho = 0, F = G = R = 0).  In: the lane's row (al, be, gaE, rho) and fgr.
 // Out: lv (x_last(lane) = y - P z1 + X z2) and, valid on EVERY lane, the group's row and fgr.
+// STEPS: PCR steps, 2^STEPS >= m (after s steps a row only couples to rows 2^s away: none left in the group)
+template <int STEPS = 5>
 __device__ __forceinline__ Lvl group_up(int m, int lane, double &al, double &be, double &ga, double &rho,
                                         double &F, double &G, double &R) {
     // close the interior couplings with the next partition's fgr
@@ -134,9 +135,9 @@ __device__ __forceinline__ Lvl group_up(int m, int lane, double &al, double &be,
         const double inv = rcp(b_);
         a_ *= inv; g_ *= inv; r0 *= inv; r1 *= inv; r2 *= inv; b_ = 1.0;
     }
-    pcr_step3(a_, b_, g_, r0, r1, r2, 4);
-    pcr_step3(a_, b_, g_, r0, r1, r2, 8);
-    pcr_step3(a_, b_, g_, r0, r1, r2, 16);
+    if (STEPS > 2) pcr_step3(a_, b_, g_, r0, r1, r2, 4);
+    if (STEPS > 3) pcr_step3(a_, b_, g_, r0, r1, r2, 8);
+    if (STEPS > 4) pcr_step3(a_, b_, g_, r0, r1, r2, 16);
     const double inv = rcp(b_);
     Lvl lv;
     lv.y = r0 * inv; lv.z1 = r1 * inv; lv.z2 = r2 * inv;
@@ -265,6 +266,8 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
     double *s_grp = s_dec + 10;             // MULTI: [5][8] rows + fgr of the groups of 32 CTAs
     double *s_gx = s_grp + 40;              // MULTI: [6]: x_last of group g at [g + 1], [0] = the rank's P
     int *s_abort = reinterpret_cast<int *>(s_gx + 8);
+    double *s_meta = s_gx + 10;             // [4]: norm partials of the CTA's last update, its edge states (travel with the next rows)
+    double *s_lc = s_meta + 4;              // [FW][3]: warp 0's CTA-level y, z1, z2 (kept out of the registers of 15 other warps)
     double *s_rows = s_x + 512;             // [G][LL_VALUES]: what every CTA published for this synchronisation
     unsigned int *s_rows32 = reinterpret_cast<unsigned int *>(s_rows);
 
@@ -283,10 +286,11 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
     unsigned int xe = 0u;
     if (MULTI) xe = (unsigned int)*reinterpret_cast<const volatile unsigned long long *>(p.peer[p.rank] + PX_EPOCH);
 
-    double *t_h6 = p.g_h6 + (size_t)cta * (FM + 1) * FT + tid;
-    double *t_hfs = p.g_hfs + (size_t)cta * (FM + 1) * FT + tid;
-    double *t_atf = p.g_atf + (size_t)cta * FNODES + tid;
-    double *t_bn = p.g_bn + (size_t)cta * FNODES + tid;
+    // one pointer, constant offsets: the four per-thread scratch arrays of this CTA are contiguous
+    double *t_h6 = p.g_thr + (size_t)cta * ((4 * FM + 2) * FT) + tid;
+    double *t_hfs = t_h6 + (FM + 1) * FT;
+    double *t_atf = t_hfs + (FM + 1) * FT;
+    double *t_bn = t_atf + FNODES;
     double *t_cs = s_cs + tid, *t_rs = s_rs + tid, *t_fs = s_fs + tid;
 
     // ---- mesh constants of this thread's elements (jj = -1 .. FM-1), once ----------------------
@@ -335,7 +339,6 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
             }
         }
         double sd = 0.0, su = 0.0, uL = 0.0, uR = 0.0;
-        double m_pa = 0.0, m_pb = 0.0, m_eF = 0.0, m_eL = 0.0;   // warp 0: norm partials of the CTA's last update, its edge states
 
         // After an update, inside the CTA: the neighbours' edge states through shuffles / shared memory, the CTA's norm
         // partials and own edge states into warp 0 (they travel with the next rows); the states just outside the CTA are
@@ -345,10 +348,11 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
             if (lane == 0) { s_red[4 * warp + 0] = psd; s_red[4 * warp + 1] = psu; s_red[4 * warp + 2] = u[0]; }
             if (lane == 31) s_red[4 * warp + 3] = u[FM - 1];
             __syncthreads();
-            if (warp == 0) {
+            if (tid == 0) {
                 double a = 0.0, b = 0.0;
+#pragma unroll
                 for (int w = 0; w < FW; ++w) { a += s_red[4 * w]; b += s_red[4 * w + 1]; }
-                m_pa = a; m_pb = b; m_eF = s_red[2]; m_eL = s_red[4 * (FW - 1) + 3];
+                s_meta[0] = a; s_meta[1] = b; s_meta[2] = s_red[2]; s_meta[3] = s_red[4 * (FW - 1) + 3];
             }
             uL = shfl_up(u[FM - 1], 1);
             uR = shfl_down(u[0], 1);
@@ -363,14 +367,15 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
         // of this CTA in s_wx, and the states just outside the CTA: s_dec[4], s_dec[5] as the neighbours hold them now,
         // s_dec[2], s_dec[3] with this solve's correction added (x_last of the CTA before, x_first of the CTA after —
         // what the neighbours will hold after applying this solve).
-        auto sync_step = [&](double a2, double b2, double g2, double r2, double F2, double G2, double R2, const Lvl &lc) -> bool {
+        auto sync_step = [&](double a2, double b2, double g2, double r2, double F2, double G2, double R2) -> bool {
             const unsigned int ep = ++nsync;   // tags start at 1: the buffer is zeroed at launch
             unsigned long long *slots = p.g_ll + (size_t)(ep & 1u) * ((size_t)G * LL_STRIDE);
             if (warp == 0 && lane < LL_WORDS) {
                 const int vi = lane >> 1;
                 double d = a2;
                 d = vi == 1 ? b2 : d; d = vi == 2 ? g2 : d; d = vi == 3 ? r2 : d; d = vi == 4 ? F2 : d; d = vi == 5 ? G2 : d;
-                d = vi == 6 ? R2 : d; d = vi == 7 ? m_pa : d; d = vi == 8 ? m_pb : d; d = vi == 9 ? m_eF : d; d = vi == 10 ? m_eL : d;
+                d = vi == 6 ? R2 : d;
+                if (vi >= 7) d = s_meta[vi - 7];
                 const unsigned int half = (lane & 1) ? (unsigned int)__double2hiint(d) : (unsigned int)__double2loint(d);
                 st_gpu_u64(slots + (size_t)cta * LL_STRIDE + lane, ((unsigned long long)ep << 32) | half);
             }
@@ -431,7 +436,7 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
                         const double *d = s_grp + 8 * lane;
                         a4 = d[0]; b4 = d[1]; g4 = d[2]; r4 = d[3]; F4 = d[4]; G4 = d[5]; R4 = d[6];
                     }
-                    const Lvl l2 = group_up(ng, lane, a4, b4, g4, r4, F4, G4, R4);   // -> the rank's row + fgr
+                    const Lvl l2 = group_up<3>(ng, lane, a4, b4, g4, r4, F4, G4, R4);   // -> the rank's row + fgr
                     // the rank's norm partials, fixed order: lane l takes CTAs 5 l .. 5 l + 4, then a butterfly
                     double ra = 0.0, rb = 0.0;
                     for (int c = 5 * lane; c < 5 * lane + 5 && c < G; ++c) { ra += s_rows[LL_VALUES * c + 7]; rb += s_rows[LL_VALUES * c + 8]; }
@@ -450,7 +455,8 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
                     // with nothing left (P = 0) or right (ga = 0) of the mesh gives x_last of the last rank
                     double a5 = 0.0, b5 = 1.0, g5 = 0.0, r5 = 0.0, F5 = 0.0, G5 = 0.0, R5 = 0.0;
                     if (lane < p.R) { a5 = v[0]; b5 = v[1]; g5 = v[2]; r5 = v[3]; F5 = v[4]; G5 = v[5]; R5 = v[6]; }
-                    const Lvl l3 = group_up(p.R, lane, a5, b5, g5, r5, F5, G5, R5);
+                    const Lvl l3 = group_up<3>(p.R, lane, a5, b5, g5, r5, F5, G5, R5);
+                    static_assert(FRMAX <= 8 && FGMAX <= 8 * 32, "rank-level groups: three PCR steps");
                     const double Xtop = r5 * rcp(b5);
                     const double xr = fma(Xtop, l3.z2, l3.y);          // x_last of rank `lane`
                     double Pr = shfl_idx(xr, p.rank > 0 ? p.rank - 1 : 0);
@@ -507,18 +513,24 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
                 if (lane == 0) s_top[0] = 0.0;
                 __syncwarp();
                 FINE_MARK(8);
-
-                // norms of the previous update, fixed order: lane l takes CTAs 5 l .. 5 l + 4, then a butterfly
-                double a = 0.0, b = 0.0;
-                for (int c = 5 * lane; c < 5 * lane + 5 && c < G; ++c) { a += s_rows[LL_VALUES * c + 7]; b += s_rows[LL_VALUES * c + 8]; }
-                warp_sum_pair(a, b);
-                if (lane == 0) { s_dec[0] = a; s_dec[1] = b; s_dec[6] = 0.0; s_dec[7] = 0.0; s_dec[8] = 0.0; }
+                if (lane == 0) { s_dec[6] = 0.0; s_dec[7] = 0.0; s_dec[8] = 0.0; }
                 __syncwarp();
+            }
+            if (!MULTI && warp == 1) {
+                // beside it, warp 1: norms of the previous update, fixed order: lane l takes CTAs 5 l .. 5 l + 4, then a butterfly
+                double a = 0.0, b = 0.0;
+#pragma unroll
+                for (int j = 0; j < 5; ++j) {
+                    const int c = 5 * lane + j;
+                    if (c < G) { a += s_rows[LL_VALUES * c + 7]; b += s_rows[LL_VALUES * c + 8]; }
+                }
+                warp_sum_pair(a, b);
+                if (lane == 0) { s_dec[0] = a; s_dec[1] = b; }
             }
             if (warp == 0) {
                 // CTA level, downwards: x_last of every warp; the states just outside the CTA
                 const double Pc = s_top[cta], Xc = s_top[cta + 1];
-                if (lane < FW) s_wx[lane + 1] = fma(Xc, lc.z2, fma(-Pc, lc.z1, lc.y));
+                if (lane < FW) s_wx[lane + 1] = fma(Xc, s_lc[3 * lane + 2], fma(-Pc, s_lc[3 * lane + 1], s_lc[3 * lane]));
                 if (lane == 0) {
                     s_wx[0] = Pc;
                     const double tL = cta > 0 ? s_rows[LL_VALUES * (cta - 1) + 10] : s_dec[6];
@@ -546,8 +558,8 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
         // sample start: one synchronisation with identity rows brings the neighbours' edge states
         cta_edges(0.0, 0.0, 4, 5);
         {
-            Lvl li; li.y = 0.0; li.z1 = 0.0; li.z2 = 0.0;
-            if (!sync_step(0.0, 1.0, 0.0, 0.0, 0.0, 0.0, 0.0, li)) return;
+            if (tid < FW) { s_lc[3 * tid] = 0.0; s_lc[3 * tid + 1] = 0.0; s_lc[3 * tid + 2] = 0.0; }
+            if (!sync_step(0.0, 1.0, 0.0, 0.0, 0.0, 0.0, 0.0)) return;
             adopt_edges();
         }
 
@@ -635,17 +647,18 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
                 __syncthreads();
                 FINE_MARK(2);
                 // ================= CTA level (warp 0) ==============================================
-                Lvl lc; lc.y = 0.0; lc.z1 = 0.0; lc.z2 = 0.0;
                 double a2 = 0.0, b2 = 1.0, g2 = 0.0, r2 = 0.0, F2 = 0.0, G2 = 0.0, R2 = 0.0;
                 if (warp == 0) {
                     if (lane < FW) {
                         const double *d = s_wrow + 8 * lane;
                         a2 = d[0]; b2 = d[1]; g2 = d[2]; r2 = d[3]; F2 = d[4]; G2 = d[5]; R2 = d[6];
                     }
-                    lc = group_up(FW, lane, a2, b2, g2, r2, F2, G2, R2);
+                    const Lvl lc = group_up<4>(FW, lane, a2, b2, g2, r2, F2, G2, R2);
+                    if (lane < FW) { s_lc[3 * lane] = lc.y; s_lc[3 * lane + 1] = lc.z1; s_lc[3 * lane + 2] = lc.z2; }
+                    static_assert(FW <= 16, "CTA-level group: four PCR steps");
                 }
                 FINE_MARK(3);
-                if (!sync_step(a2, b2, g2, r2, F2, G2, R2, lc)) return;
+                if (!sync_step(a2, b2, g2, r2, F2, G2, R2)) return;
                 if (k > 0 && !(sd > p.tol2 * su && k < p.kmax)) { adopt_edges(); break; }
                 // ================= warp level, downwards; back-substitution, update, norms ========
                 double psd = 0.0, psu = 0.0;
@@ -692,7 +705,7 @@ constexpr size_t fine_smem(int fm) { return sizeof(double) * (3 * (size_t)fm * F
 
 struct FinePlan {
     int G;
-    size_t off_h6, off_hfs, off_atf, off_bn, off_ll, ll_bytes, total;
+    size_t off_thr, off_ll, ll_bytes, total;
 };
 
 static int fine_plan(int N, int fm, FinePlan &pl) {
@@ -700,10 +713,7 @@ static int fine_plan(int N, int fm, FinePlan &pl) {
     pl.G = (N + nodes - 1) / nodes;
     size_t o = 256;
     auto take = [&](size_t doubles) { size_t at = o; o += sizeof(double) * doubles; o = (o + 255) & ~(size_t)255; return at; };
-    pl.off_h6 = take((size_t)pl.G * (fm + 1) * FT);
-    pl.off_hfs = take((size_t)pl.G * (fm + 1) * FT);
-    pl.off_atf = take((size_t)pl.G * nodes);
-    pl.off_bn = take((size_t)pl.G * nodes);
+    pl.off_thr = take((size_t)pl.G * (4 * fm + 2) * FT);
     pl.off_ll = take(2 * (size_t)pl.G * LL_STRIDE);   // double-buffered by the parity of the synchronisation
     pl.ll_bytes = sizeof(unsigned long long) * 2 * (size_t)pl.G * LL_STRIDE;
     pl.total = o;
@@ -746,10 +756,7 @@ static int fine_launch_rows(FineParams &p, void *workspace, cudaStream_t st, int
     char *ws = static_cast<char *>(workspace);
     p.G = pl.G;
     p.bar = reinterpret_cast<unsigned long long *>(ws);
-    p.g_h6 = reinterpret_cast<double *>(ws + pl.off_h6);
-    p.g_hfs = reinterpret_cast<double *>(ws + pl.off_hfs);
-    p.g_atf = reinterpret_cast<double *>(ws + pl.off_atf);
-    p.g_bn = reinterpret_cast<double *>(ws + pl.off_bn);
+    p.g_thr = reinterpret_cast<double *>(ws + pl.off_thr);
     p.g_ll = reinterpret_cast<unsigned long long *>(ws + pl.off_ll);
     BX_CUDA(cudaMemsetAsync(p.bar, 0, 256, st));
     BX_CUDA(cudaMemsetAsync(p.g_ll, 0, pl.ll_bytes, st));
