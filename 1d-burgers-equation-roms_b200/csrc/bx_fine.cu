@@ -72,6 +72,10 @@ struct FineParams {
 
 struct Lvl { double y, z1, z2; };
 
+__device__ __forceinline__ void cp_async8(unsigned int smem_addr, const double *gptr) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_addr), "l"(gptr) : "memory");
+}
+
 // BX_FINE_TRACE (experiments, tools/fine_trace.py): cycles of thread 0 of CTA 0 between marks, summed per mark
 #ifdef BX_FINE_TRACE
 __device__ unsigned long long g_fine_trace[32];
@@ -270,6 +274,9 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
     double *s_lc = s_meta + 4;              // [FW][3]: warp 0's CTA-level y, z1, z2 (kept out of the registers of 15 other warps)
     double *s_rows = s_x + 512;             // [G][LL_VALUES]: what every CTA published for this synchronisation
     unsigned int *s_rows32 = reinterpret_cast<unsigned int *>(s_rows);
+    // the same bytes, between synchronisations: ring of two row stages [stage][h6R | hfs | bn][tid] that streams the
+    // thread's per-row constants from the L2-resident scratch two rows ahead of the sweep (cp.async: no registers held)
+    double *s_ring = s_rows + threadIdx.x;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int cta = blockIdx.x, G = p.G, N = p.N;
@@ -302,6 +309,24 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
     }
 
     if (MULTI && tid == 0) *s_abort = 0;
+    // (measured: the ring pays at 16 rows per thread, 15.4 -> 14.1 us per iteration; with 8 or 4 rows the compiler has the
+    // registers to hoist the plain loads itself and the ring only adds instructions: 6.3 -> 6.8 us at 4 rows)
+    constexpr bool RING = FM >= 16;
+    const unsigned int ring_sa = (unsigned int)__cvta_generic_to_shared(s_ring);
+    auto ring_issue = [&](int j) {   // row j -> stage j & 1
+        const unsigned int dst = ring_sa + (unsigned int)((j & 1) * 3 * FT * 8);
+        cp_async8(dst, t_h6 + (j + 1) * FT);
+        cp_async8(dst + FT * 8, t_hfs + (j + 1) * FT);
+        cp_async8(dst + 2 * FT * 8, t_bn + j * FT);
+    };
+    auto ring_start = [&]() {   // rows 0 and 1 of the next sweep
+        if (!RING) return;
+        asm volatile("cp.async.wait_all;" ::: "memory");
+        ring_issue(0);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        ring_issue(1);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
     const bool leftv = node0 > 0 && jl >= 0;
     const double a6L = leftv ? a6 : 0.0, c1L = leftv ? c1 : 0.0;
 
@@ -581,6 +606,8 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
             // discarded when update k turns out to have converged (or reached kmax).  u is only ever changed by confirmed
             // iterations, so states and counts are those of the reference loop.
             int k = 0;
+            if (RING) __threadfence_block();   // this thread's bn stores before its asynchronous copies of them
+            ring_start();
             FINE_MARK(13);
             for (;;) {
                 // ================= thread level: assemble + sweep (:667-692) ======================
@@ -599,7 +626,15 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
                     double csj = 0.0, rsj = 0.0, fsj = 0.0;
 #pragma unroll
                     for (int j = 0; j < FM; ++j) {
-                        const double h6R = t_h6[(j + 1) * FT];
+                        double h6R, hfsj, bnj;
+                        if (RING) {
+                            asm volatile("cp.async.wait_group 1;" ::: "memory");   // row j has landed (row j + 1 may be in flight)
+                            h6R = s_ring[(j & 1) * 3 * FT]; hfsj = s_ring[(j & 1) * 3 * FT + FT]; bnj = s_ring[(j & 1) * 3 * FT + 2 * FT];
+                            if (j + 2 < FM) ring_issue(j + 2);
+                            asm volatile("cp.async.commit_group;" ::: "memory");
+                        } else {
+                            h6R = t_h6[(j + 1) * FT]; hfsj = t_hfs[(j + 1) * FT]; bnj = t_bn[j * FT];
+                        }
                         const double um = (j == 0) ? uL : u[j > 0 ? j - 1 : 0];
                         const double up = (j == FM - 1) ? uR : u[j < FM - 1 ? j + 1 : j];
                         const double u1 = u[j], u2 = up;
@@ -607,7 +642,7 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
                         const double tt = a6 * sm;
                         double pe = fma(a6, u1, tt);
                         double qe = fma(a6, u2, tt);
-                        const double z = fma(sm * (u2 - u1), 1.0 / 6.0, -t_hfs[(j + 1) * FT]);
+                        const double z = fma(sm * (u2 - u1), 1.0 / 6.0, -hfsj);
                         double Ge = (c1 * rcp(fmax(fabs(sm), 2.0e-10))) * z;
                         if (j >= jl) { pe = 0.0; qe = 0.0; Ge = 0.0; }   // no element to the right of node N-1
                         double keL = 0.0, keR = 0.0;
@@ -618,7 +653,7 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
                         double a = (h6L - keL) - qL;
                         double c = (h6R - keR) + pe;
                         double b = (2.0 * (h6L + h6R) + (keL + keR)) + (qL - pe);
-                        double r = (t_bn[j * FT] - GL + Ge) - fma(a, um, fma(b, u1, c * u2));
+                        double r = (bnj - GL + Ge) - fma(a, um, fma(b, u1, c * u2));
                         if (j > jl) { a = 0.0; b = 1.0; c = 0.0; r = 0.0; }              // padded row
                         if (j == 0 && node0 == 0) { a = 0.0; b = 1.0; c = 0.0; r = mu1 - u1; }   // Dirichlet row (:679-686)
                         ct.row(j, a, b, c, r, csj, rsj, fsj);
@@ -660,6 +695,7 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
                 FINE_MARK(3);
                 if (!sync_step(a2, b2, g2, r2, F2, G2, R2)) return;
                 if (k > 0 && !(sd > p.tol2 * su && k < p.kmax)) { adopt_edges(); break; }
+                ring_start();   // for the next sweep, while this iteration is finished (bn does not change inside a step)
                 // ================= warp level, downwards; back-substitution, update, norms ========
                 double psd = 0.0, psu = 0.0;
                 {
@@ -701,7 +737,9 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
         *reinterpret_cast<volatile unsigned long long *>(p.peer[p.rank] + PX_EPOCH) = xe;
 }
 
-constexpr size_t fine_smem(int fm) { return sizeof(double) * (3 * (size_t)fm * FT + 512 + (size_t)FGMAX * LL_VALUES); }
+// swept rows (3 x nodes) | exchange area (512) | the rows of all CTAs, aliased with the two-stage constant ring (2 x 3 x FT)
+constexpr size_t fine_smem(int fm) { return sizeof(double) * (3 * (size_t)fm * FT + 512 + 2 * 3 * (size_t)FT); }
+static_assert(2 * 3 * FT >= FGMAX * LL_VALUES, "the ring covers the row area");
 
 struct FinePlan {
     int G;
