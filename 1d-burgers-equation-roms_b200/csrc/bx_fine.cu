@@ -2,34 +2,46 @@
 // mesh far larger than one warp can hold (BASELINE config 5: 2^20 nodes, one trajectory).
 //
 // ONE persistent cooperative kernel integrates the whole trajectory.  The mesh is cut into
-// contiguous partitions three levels deep — 16 nodes per thread, 32 threads per warp, 16 warps per
-// CTA (8192 nodes), G = ceil(N / 8192) CTAs — and each Picard iteration solves the N x N tridiagonal
-// system A delta = -R by a partition (SPIKE / cyclic-reduction type) method on that hierarchy:
-//   thread  assembles its 16 rows from the closed forms of the 2-point-Gauss element integrals
+// contiguous partitions three levels deep — FM nodes per thread (16, 8 or 4: the fewest whose CTAs are all
+// co-resident), 32 threads per warp, 16 warps per CTA, G = ceil(N / (512 FM)) CTAs — and each Picard iteration
+// solves the N x N tridiagonal system A delta = -R by a partition (SPIKE / cyclic-reduction type) method on that
+// hierarchy:
+//   thread  assembles its FM rows from the closed forms of the 2-point-Gauss element integrals
 //           (as bx_fom.cu), sweeps them in continuant form carrying the coupling to the previous
 //           partition's last unknown P, and condenses to
 //              row:  al P + be x_last + ga E = rho      (E = first unknown of the next partition)
 //              fgr:  x_first = R - F P - G x_last
 //   warp / CTA   "group_up": neighbours' fgr close the interior couplings (E -> x_last of the next
-//           partition), a 32-lane parallel cyclic reduction with three right-hand sides solves the
+//           partition), a parallel cyclic reduction with three right-hand sides solves the
 //           group's rows for  x_last(j) = y_j - P z1_j + X z2_j  (P, X: the group's own boundary
 //           unknowns), and the group's row / fgr follow by substitution;
-//   grid    every CTA publishes one row + fgr (7 doubles); after a grid barrier each CTA solves the
-//           G-row closed system redundantly (5 rows per lane + warp PCR) and walks back down.
-// Then local back-substitution, update, |delta|^2 and |U|^2; a second grid barrier carries the norm
-// partials (summed in CTA order: every CTA takes the same decision) and the partition-edge states.
-// U_k lives in registers and the swept rows (cs, rs, fs) in shared memory (192 KB) for the whole
-// trajectory; mesh / forcing constants and M U^n + At F stream from an L2-resident scratch in a
-// [row][thread] interleaved layout (coalesced).  HBM traffic: the 8N-byte snapshot per time step.
+//   grid    every CTA publishes its row + fgr, waits for those of all CTAs, solves the G-row closed system
+//           redundantly (5 rows per lane + warp PCR) and walks back down.
+// Then local back-substitution, update, |delta|^2 and |U|^2.
+//
+// ONE synchronisation of the grid per Picard iteration, and no grid barrier:
+//   * the norm partials and the partition-edge states of update k travel WITH the rows of iteration k + 1: the
+//     convergence test runs one synchronisation late, so the front half of k + 1 (assembly, sweeps, condensation) is
+//     speculative and is discarded when update k had converged or reached kmax (one front half per time step;
+//     u is only changed by confirmed iterations: states and counts are those of the reference loop);
+//   * the states just outside a CTA need no exchange of their own: they are the neighbours' published edge states plus
+//     the interface solution every CTA has anyway (x_last of the CTA before, x_first = R - F P - G x_last of the one after);
+//   * what a CTA publishes (11 doubles) travels as 22 epoch-tagged 8-byte words; every thread polls its share of the
+//     G x 22 words into shared memory — no fence, no atomic counter, no second read of L2 (see "synchronisation" below).
+// Measured on B200, 2^20 nodes: 19.3 us per Picard iteration with two grid barriers -> 13.8 us (profiles/r4*).
+//
+// U_k lives in registers and the swept rows (cs, rs, fs) in shared memory (3 x 8 x 512 FM bytes) for the whole
+// trajectory; mesh / forcing constants and M U^n + At F stream from an L2-resident scratch in a [row][thread]
+// interleaved layout (coalesced) — at FM = 16 through a two-stage cp.async ring.  HBM traffic: the 8N-byte snapshot
+// per time step.
 //
 // MULTI (bx_fom_picard_finemesh_ranks): the trajectory is cut once more, into R <= 8 contiguous node blocks, one per
 // GPU (one process per GPU), and the solve gets a FOURTH level: every CTA of a rank folds the rank's CTA rows into
-// ONE row + fgr (two group_up stages: 32 CTAs per warp, then the <= 5 groups), CTA 0 stores that row (7 doubles)
-// straight into every rank's exchange buffer through peer memory (NVLink; cudaIpc-mapped) and releases a flag, every
-// CTA acquires the R flags in its OWN buffer, solves the R-row closed system redundantly and walks back down.  A
-// second exchange of the same kind carries the norm partials (summed in rank order: every CTA of every rank takes
-// the same decision) and the block-edge states.  No collective library on the data path, no host round trip; the
-// state of a rank never leaves its GPU.  Meshes up to R x 148 x 8192 nodes.
+// ONE row + fgr (two group_up stages: 32 CTAs per warp, then the <= 5 groups), CTA 0 stores it, with the rank's norm
+// partials and block-edge states (11 doubles as 22 tagged words), straight into every rank's exchange buffer through
+// peer memory (NVLink; cudaIpc-mapped), every CTA polls the R slots in its OWN buffer, solves the R-row closed system
+// redundantly and walks back down.  One NVLink crossing per Picard iteration, no collective library on the data path,
+// no host round trip; the state of a rank never leaves its GPU.  Meshes up to R x 148 x 8192 nodes.
 #include "bx_common.cuh"
 #include <cstdint>
 #include <cstring>
@@ -165,7 +177,7 @@ __device__ __forceinline__ Lvl group_up(int m, int lane, double &al, double &be,
 // after it has seen epoch e + 1 of every CTA, which they publish after all their threads have read epoch e.
 constexpr int LL_VALUES = 11;
 constexpr int LL_WORDS = 2 * LL_VALUES;
-constexpr int LL_STRIDE = 32;     // words per CTA slot (256 bytes)
+constexpr int LL_STRIDE = LL_WORDS;   // words per CTA slot: packed, word 22 c + w of a synchronisation sits at [22 c + w]
 __device__ __forceinline__ void st_gpu_u64(unsigned long long *a, unsigned long long v) {
     asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(a), "l"(v) : "memory");
 }
@@ -417,10 +429,7 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
 #pragma unroll
                     for (int q = 0; q < MAXW; ++q) {
                         const int idx = tid + q * FT;
-                        if (idx < total) {
-                            const int c = idx / LL_WORDS;
-                            wd[q] = ld_gpu_u64(slots + (size_t)c * LL_STRIDE + (idx - c * LL_WORDS));
-                        }
+                        if (idx < total) wd[q] = ld_gpu_u64(slots + idx);
                     }
 #pragma unroll
                     for (int q = 0; q < MAXW; ++q)
