@@ -148,7 +148,8 @@ int bx_fom_picard_trajectories_noalloc(int B, int N, int nsteps, const double *X
 /* FEMBurgers.fom_burgers, FEM/fem_burgers.py:646-707, on a mesh too large for one warp (N > 1024;
  * BASELINE config 5: 2^20 nodes): one persistent cooperative kernel per call, the N x N tridiagonal solve
  * of every Picard iteration done by a three-level partition / cyclic-reduction method across threads,
- * warps and CTAs (two grid barriers per iteration), state on chip for the whole trajectory.  The B samples
+ * warps and CTAs (one synchronisation of the grid per iteration, by epoch-tagged words instead of a barrier), 4, 8
+ * or 16 mesh rows per thread by mesh size (BX_TUNE_FINE_ROWS), state on chip for the whole trajectory.  The B samples
  * are integrated one after the other.  Same arguments and outputs as bx_fom_picard_trajectories.
  * N <= 8192 * min(SM count, 160).  workspace: bx_fine_workspace_bytes(N) bytes, contents ignored.       */
 long long bx_fine_workspace_bytes(int N);
