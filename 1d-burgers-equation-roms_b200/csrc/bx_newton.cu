@@ -59,12 +59,25 @@ __device__ __forceinline__ void warp_pcr2(double al, double be, double ga, doubl
     r1 *= inv; r2 *= inv;
 }
 
+// the four swept-row arrays (cs, ys, zs, fs) of a lane: registers up to 16 rows per lane; at 32 rows per lane (N > 512)
+// they would need 256 registers beside u[32] (round 1: 1640 bytes of stack, 3.5 KB of spill traffic per iteration), so
+// they live in the warp's shared memory instead ([array][row][lane]: conflict-free)
+template <int M> struct NewtonShape { static constexpr bool ROWS_IN_SMEM = M > 16; };
+
 template <int M> struct NewtonSmem {
     static constexpr int EL = (M + 1) * 32;
     static constexpr int NL = M * 32;
     static constexpr int MESH = 2 * EL + NL;   // off, h6 | dg
-    static constexpr int PER_WARP = 2 * NL;    // AtF, bn
+    static constexpr int PER_WARP = 2 * NL + (NewtonShape<M>::ROWS_IN_SMEM ? 4 * NL : 0);   // AtF, bn | cs, ys, zs, fs
     static constexpr size_t bytes(int warps) { return sizeof(double) * (MESH + (size_t)warps * PER_WARP); }
+};
+
+template <int M, bool SMEM> struct RowStore {
+    double r[SMEM ? 1 : M];
+    double *s;   // SMEM: this lane's column of the warp's [row][lane] array
+    __device__ __forceinline__ void set(int j, double v) { if (SMEM) s[j * 32] = v; else r[SMEM ? 0 : j] = v; }
+    // volatile: keeps the 4 x 32 loads of an unrolled sweep where they are used instead of hoisted into registers
+    __device__ __forceinline__ double get(int j) const { return SMEM ? *reinterpret_cast<volatile double *>(s + j * 32) : r[SMEM ? 0 : j]; }
 };
 
 template <int M, int WARPS>
@@ -168,7 +181,9 @@ __global__ void __launch_bounds__(WARPS * 32, 1) fom_newton_kernel(const NewtonP
             double sd, su;
             do {
                 const double uL = shfl_up(u[M - 1], 1), uR = shfl_down(u[0], 1);
-                double cs[M], ys[M], zs[M], fs[M];
+                constexpr bool RS = NewtonShape<M>::ROWS_IN_SMEM;
+                RowStore<M, RS> cs, ys, zs, fs;
+                cs.s = w_bn + L::NL + lane; ys.s = cs.s + L::NL; zs.s = ys.s + L::NL; fs.s = zs.s + L::NL;
                 // continuant recurrences (see Continuant in bx_common.cuh), two right-hand sides
                 double thm1 = 1.0, thm2 = 1.0, r1m = 0.0, r2m = 0.0, phm = 0.0, cm1 = 0.0;
                 double offL = s_off[lane];
@@ -201,26 +216,27 @@ __global__ void __launch_bounds__(WARPS * 32, 1) fom_newton_kernel(const NewtonP
                         ct = c * thm1;
                     }
                     const double inv = rcp(th);
-                    cs[j] = ct * inv; ys[j] = r1 * inv; zs[j] = r2 * inv; fs[j] = ph * inv;
+                    cs.set(j, ct * inv); ys.set(j, r1 * inv); zs.set(j, r2 * inv); fs.set(j, ph * inv);
                     thm2 = thm1; thm1 = th; r1m = r1; r2m = r2; phm = ph; cm1 = c;
                     offL = off; qL = qe;
                 }
                 // condensation to one row per lane (rows: fs P + x_j + cs x_{j+1} = ys | zs)
                 double F = 0.0, G = 0.0, Y = 0.0, Z = 0.0;
                 if (M >= 2) {
-                    F = fs[M - 2]; G = cs[M - 2]; Y = ys[M - 2]; Z = zs[M - 2];
+                    F = fs.get(M - 2); G = cs.get(M - 2); Y = ys.get(M - 2); Z = zs.get(M - 2);
 #pragma unroll
                     for (int j = M - 3; j >= 0; --j) {
-                        F = fma(-cs[j], F, fs[j]);
-                        G = -cs[j] * G;
-                        Y = fma(-cs[j], Y, ys[j]);
-                        Z = fma(-cs[j], Z, zs[j]);
+                        const double cj = cs.get(j);
+                        F = fma(-cj, F, fs.get(j));
+                        G = -cj * G;
+                        Y = fma(-cj, Y, ys.get(j));
+                        Z = fma(-cj, Z, zs.get(j));
                     }
                 }
                 const double Fn = shfl_down(F, 1), Gn = shfl_down(G, 1), Yn = shfl_down(Y, 1), Zn = shfl_down(Z, 1);
-                const double cl = (lane == 31) ? 0.0 : cs[M - 1];
-                const double al = (lane == 0) ? 0.0 : fs[M - 1];
-                double yl = fma(-cl, Yn, ys[M - 1]), zl = fma(-cl, Zn, zs[M - 1]);
+                const double cl = (lane == 31) ? 0.0 : cs.get(M - 1);
+                const double al = (lane == 0) ? 0.0 : fs.get(M - 1);
+                double yl = fma(-cl, Yn, ys.get(M - 1)), zl = fma(-cl, Zn, zs.get(M - 1));
                 warp_pcr2(al, fma(-cl, Fn, 1.0), -cl * Gn, yl, zl);
                 double Py = shfl_up(yl, 1), Pz = shfl_up(zl, 1);
                 if (lane == 0) { Py = 0.0; Pz = 0.0; }
@@ -230,10 +246,11 @@ __global__ void __launch_bounds__(WARPS * 32, 1) fom_newton_kernel(const NewtonP
 #pragma unroll
                 for (int j = M - 1; j >= 0; --j) {
                     if (j < M - 1) {
-                        y = fma(-cs[j], y, fma(-fs[j], Py, ys[j]));
-                        z = fma(-cs[j], z, fma(-fs[j], Pz, zs[j]));
+                        const double cj = cs.get(j), fj = fs.get(j);
+                        y = fma(-cj, y, fma(-fj, Py, ys.get(j)));
+                        z = fma(-cj, z, fma(-fj, Pz, zs.get(j)));
                     }
-                    ys[j] = y; zs[j] = z;
+                    ys.set(j, y); zs.set(j, z);
                     const int i = node0 + j;
                     const double um = (j == 0) ? uL : u[j > 0 ? j - 1 : 0];
                     const double up = (j == M - 1) ? uR : u[j < M - 1 ? j + 1 : j];
@@ -248,7 +265,7 @@ __global__ void __launch_bounds__(WARPS * 32, 1) fom_newton_kernel(const NewtonP
                 sd = 0.0; su = 0.0;
 #pragma unroll
                 for (int j = 0; j < M; ++j) {
-                    const double delta = fma(-zs[j], beta, ys[j]);
+                    const double delta = fma(-zs.get(j), beta, ys.get(j));
                     const double un = fma(p.lambda, delta, u[j]);
                     const double d = un - u[j];
                     sd = fma(d, d, sd);
