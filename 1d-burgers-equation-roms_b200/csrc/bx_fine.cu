@@ -622,7 +622,7 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
                 // ================= thread level: assemble + sweep (:667-692) ======================
                 double al, be, ga, rho, F, Gc, R;
                 {
-                    Continuant<FM> ct;
+                    Continuant<FM, true> ct;   // 1-ulp reciprocals (3 DFMA), as in the FOM sweep kernels
                     double h6L = t_h6[0];
                     double qL, GL;
                     {
@@ -630,7 +630,7 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
                         const double sm = u1 + u2;
                         qL = fma(a6L, u2, a6L * sm);
                         const double z = fma(sm * (u2 - u1), 1.0 / 6.0, -t_hfs[0]);
-                        GL = (c1L * rcp(fmax(fabs(sm), 2.0e-10))) * z;
+                        GL = (c1L * rcp1(fmax(fabs(sm), 2.0e-10))) * z;
                     }
                     double csj = 0.0, rsj = 0.0, fsj = 0.0;
 #pragma unroll
@@ -652,7 +652,7 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
                         double pe = fma(a6, u1, tt);
                         double qe = fma(a6, u2, tt);
                         const double z = fma(sm * (u2 - u1), 1.0 / 6.0, -hfsj);
-                        double Ge = (c1 * rcp(fmax(fabs(sm), 2.0e-10))) * z;
+                        double Ge = (c1 * rcp1(fmax(fabs(sm), 2.0e-10))) * z;
                         if (j >= jl) { pe = 0.0; qe = 0.0; Ge = 0.0; }   // no element to the right of node N-1
                         double keL = 0.0, keR = 0.0;
                         if (has_e) {
