@@ -51,25 +51,42 @@ class PeerExchange:
 
     @classmethod
     def create(cls, group=None):
+        """Collective over `group`: every rank must call it.  A rank whose allocation or mapping fails does not leave the
+        others waiting: the outcome of every local step is exchanged before the next collective step, and all ranks raise."""
         import torch.distributed as dist
         lib = _lib.load()
         R, rank = dist.get_world_size(group), dist.get_rank(group)
         if R > MAX_RANKS:
             raise ValueError(f"at most {MAX_RANKS} ranks")
+
+        def all_ok(ok, what):
+            flags = [None] * R
+            dist.all_gather_object(flags, bool(ok), group=group)
+            if not all(flags):
+                raise _lib.BurgersB200Error(f"PeerExchange.create: {what} failed on rank(s) {[r for r, f in enumerate(flags) if not f]}")
+
         own = ctypes.c_void_p()
         handle = ctypes.create_string_buffer(64)
-        _lib.check(lib.bx_peer_alloc(ctypes.byref(own), handle), "bx_peer_alloc")
+        all_ok(lib.bx_peer_alloc(ctypes.byref(own), handle) == _lib.BX_OK, "bx_peer_alloc")
         handles = [None] * R
         dist.all_gather_object(handles, bytes(handle.raw), group=group)
-        bufs, opened = [], []
+        bufs, opened, ok = [], [], True
         for r in range(R):
             if r == rank:
                 bufs.append(own.value)
                 continue
             ptr = ctypes.c_void_p()
-            _lib.check(lib.bx_peer_open(ctypes.create_string_buffer(handles[r], 64), ctypes.byref(ptr)), "bx_peer_open")
+            if lib.bx_peer_open(ctypes.create_string_buffer(handles[r], 64), ctypes.byref(ptr)) != _lib.BX_OK:
+                ok = False
+                break
             bufs.append(ptr.value); opened.append(ptr.value)
-        dist.barrier(group)
+        try:
+            all_ok(ok, "bx_peer_open (cudaIpcOpenMemHandle)")
+        except _lib.BurgersB200Error:
+            for ptr in opened:
+                lib.bx_peer_close(ptr)
+            lib.bx_peer_free(own.value)
+            raise
         return cls(rank, bufs, own.value, opened)
 
     @classmethod

@@ -13,7 +13,8 @@ shard).  One JSON line on stdout (rank 0).  Beside the headline the line carries
   * `roofline`         bound = FP64 pipe: executed FP64 flop/s of the FOM kernel against the DFMA peak measured
                        in this run (bx_probe_fp64_peak); the 88*N byte model of SURVEY 8d as `model_frac`;
   * `extra_workloads`  configs 3, 4 and 5a under the same clock: snapshot Gram + all-reduce, POD-LSPG / Galerkin
-                       PROM with 28 modes, quadratic-manifold builder + Galerkin PROM with 28 modes, fine mesh;
+                       PROM with 28 modes, quadratic-manifold builder + Galerkin PROM with 28 modes, fine mesh (one
+                       2^20-node trajectory per GPU, and at N > 1 the same trajectory PARTITIONED over the N ranks);
   * `cpu_baseline`     the oracle port on one host core over a bounded sample (rank 0, N = 1).
 See DESIGN.md "Measurement" for every field.
 """
@@ -549,28 +550,60 @@ class Bench:
         out["config4_qm_galerkin28"]["flagged_nonfinite_steps"] = self.reduce(int((iters < 0).sum().item()), "sum")
         self.launches += 2 * 2
 
-        # config 5a: one trajectory on 2^20 nodes at constant CFL (replicas only: rank 0 at N = 1)
-        if world == 1:
-            NF = 1 << 20
-            femf = self.bx.FEMBurgers(np.linspace(0.0, 100.0, NF))
-            Atf = AT * 511.0 / (NF - 1)
-            Uf = torch.empty((1, nT + 1, NF), dtype=torch.float64, device=dev)
-            itf = torch.empty((1, nT), dtype=torch.int32, device=dev)
-            u0f = torch.ones(NF, dtype=torch.float64, device=dev)
-            ms, _ = self.timed(lambda: femf.fom_burgers_batch(Atf, nT, u0f, [4.75], E, [0.02], out=Uf, iters_out=itf), 3, 1)
-            its = int(itf.sum().item())
-            ms1 = ms / 3
-            hbm_peak, _ = measured_peak_hbm()
-            out["config5a_finemesh"] = {"ms": ms1, "iterations": its, "us_per_iteration": 1e3 * ms1 / max(its, 1),
-                                        "time_steps_per_s": nT / (ms1 * 1e-3),
-                                        "model_gbs": 88.0 * NF * its / (ms1 * 1e-3) / 1e9,
-                                        "model_frac_of_hbm": 88.0 * NF * its / (ms1 * 1e-3) / 1e9 / hbm_peak,
-                                        "note": "2^20 nodes, one trajectory, constant CFL At = 0.05*511/(N-1) (5a); 88*N B per iteration is the "
-                                                "banded-dataflow model, the kernel keeps state on chip (latency-bound, see DESIGN)"}
-            self.launches += 4
-            del Uf, femf
+        # config 5a: one trajectory on 2^20 nodes at constant CFL; every rank integrates its own replica (max over ranks)
+        NF = 1 << 20
+        Xf = np.linspace(0.0, 100.0, NF)
+        femf = self.bx.FEMBurgers(Xf)
+        Atf = AT * 511.0 / (NF - 1)
+        Uf = torch.empty((1, nT + 1, NF), dtype=torch.float64, device=dev)
+        itf = torch.empty((1, nT), dtype=torch.int32, device=dev)
+        u0f = torch.ones(NF, dtype=torch.float64, device=dev)
+        ms, _ = self.timed(lambda: femf.fom_burgers_batch(Atf, nT, u0f, [4.75], E, [0.02], out=Uf, iters_out=itf), 3, 1)
+        its = int(itf.sum().item())
+        ms1 = ms / 3
+        hbm_peak, _ = measured_peak_hbm()
+        out["config5a_finemesh"] = {"ms": ms1, "iterations": its, "us_per_iteration": 1e3 * ms1 / max(its, 1),
+                                    "time_steps_per_s": nT / (ms1 * 1e-3),
+                                    "model_gbs": 88.0 * NF * its / (ms1 * 1e-3) / 1e9,
+                                    "model_frac_of_hbm": 88.0 * NF * its / (ms1 * 1e-3) / 1e9 / hbm_peak,
+                                    "note": "2^20 nodes, one trajectory per GPU, constant CFL At = 0.05*511/(N-1) (5a); 88*N B per iteration is the "
+                                            "banded-dataflow model, the kernel keeps state on chip (latency chain, see DESIGN K-Fine)"}
+        self.launches += 4
+        del Uf, femf
+        # the same trajectory PARTITIONED over the ranks: interface rows through peer memory
+        if 1 < world <= 8:
+            out["config5a_finemesh_ranks"] = self.finemesh_ranks(Xf, Atf, nT, its)
         out["peaks"] = {"dmma_tflops": dmma_peak, "dfma_tflops": dfma_peak}
         return out
+
+    def finemesh_ranks(self, Xf, Atf, nT, its_single):
+        """One 2^20-node trajectory over all ranks (bx_fom_picard_finemesh_ranks); a failure on any rank is reported by all."""
+        torch, dev = self.torch, self.dev
+        from burgers_b200.finemesh_dist import PeerExchange, fom_burgers_partitioned, node_partition
+        ex = None
+        try:
+            ex = PeerExchange.create()
+            off, cnt = node_partition(Xf.size, self.world)[self.rank]
+            outb = torch.empty((1, nT + 1, cnt), dtype=torch.float64, device=dev)
+            u0l = np.ones(cnt)
+            best = None
+            for rep in range(3):   # the first one is the warm-up
+                _, it = fom_burgers_partitioned(Xf, Atf, nT, u0l, 4.75, E, 0.02, ex, out=outb)
+                ms = self.reduce(ex.last_kernel_ms)
+                if rep > 0:
+                    best = ms if best is None else min(best, ms)
+            self.launches += 3
+            its = int(it.sum().item())
+            return {"ms": best, "iterations": its, "us_per_iteration": 1e3 * best / max(its, 1), "ranks": self.world,
+                    "nodes_per_rank": [c for _, c in node_partition(Xf.size, self.world)],
+                    "iterations_equal_single_gpu": its == its_single, "finite": bool(torch.isfinite(outb).all().item()),
+                    "note": "kernel time by CUDA events, max over ranks, best of 2 after a warm-up launch; every Picard iteration "
+                            "exchanges one interface row per rank through NVLink peer memory (no collective call inside the launch)"}
+        except Exception as e:   # noqa: BLE001 - the bench line must survive a box without IPC / peer access
+            return {"error": f"{type(e).__name__}: {e}"[:300]}
+        finally:
+            if ex is not None:
+                ex.close()
 
 
 def main():
