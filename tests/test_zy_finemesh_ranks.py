@@ -29,20 +29,22 @@ def _run_ranks(X, At, nsteps, u0, mu1, E, mu2, R, launches=1):
     ex = PeerExchange.local(R)
     try:
         Xd = torch.from_numpy(X).to(dev)
-        m1 = torch.tensor([mu1], dtype=torch.float64, device=dev)
-        m2 = torch.tensor([mu2], dtype=torch.float64, device=dev)
+        m1 = torch.tensor(np.atleast_1d(mu1), dtype=torch.float64, device=dev)
+        m2 = torch.tensor(np.atleast_1d(mu2), dtype=torch.float64, device=dev)
+        B = int(m1.numel())
+        batched = 1 if np.ndim(u0) == 2 else 0
         streams = [torch.cuda.Stream(dev) for _ in range(R)]
         keep = []
         for r, (off, cnt) in enumerate(parts):
-            u0d = torch.from_numpy(np.ascontiguousarray(u0[off:off + cnt])).to(dev)
-            U = torch.full((1, nsteps + 1, cnt), float("nan"), dtype=torch.float64, device=dev)
-            it = torch.full((1, nsteps), -7, dtype=torch.int32, device=dev)
+            u0d = torch.from_numpy(np.ascontiguousarray(u0[..., off:off + cnt])).to(dev)
+            U = torch.full((B, nsteps + 1, cnt), float("nan"), dtype=torch.float64, device=dev)
+            it = torch.full((B, nsteps), -7, dtype=torch.int32, device=dev)
             ws = torch.empty(int(lib.bx_fine_workspace_bytes(cnt)), dtype=torch.uint8, device=dev)
             keep.append((u0d, U, it, ws))
         torch.cuda.synchronize(dev)
         for r, (off, cnt) in [pr for _ in range(launches) for pr in enumerate(parts)]:
             u0d, U, it, ws = keep[r]
-            _lib.check(lib.bx_fom_picard_finemesh_ranks(1, N, off, cnt, nsteps, Xd.data_ptr(), u0d.data_ptr(), 0,
+            _lib.check(lib.bx_fom_picard_finemesh_ranks(B, N, off, cnt, nsteps, Xd.data_ptr(), u0d.data_ptr(), batched,
                                                         m1.data_ptr(), m2.data_ptr(), float(At), float(E), 1e-6, 20,
                                                         U.data_ptr(), it.data_ptr(), ws.data_ptr(), R, r,
                                                         ex[r].pointer_array(), streams[r].cuda_stream),
@@ -50,10 +52,12 @@ def _run_ranks(X, At, nsteps, u0, mu1, E, mu2, R, launches=1):
         torch.cuda.synchronize(dev)
         if any(e.failed(streams[r].cuda_stream) for r, e in enumerate(ex)):
             pytest.skip("the rank kernels were not scheduled side by side on this device (gave up after 10 s)")
-        Ufull = np.concatenate([k[1][0].cpu().numpy() for k in keep], axis=1).T
-        its = [k[2][0].cpu().numpy() for k in keep]
+        Ufull = np.concatenate([k[1].cpu().numpy() for k in keep], axis=2)     # (B, nsteps + 1, N)
+        its = [k[2].cpu().numpy() for k in keep]
         for i in its[1:]:
             assert np.array_equal(i, its[0])
+        if B == 1 and np.ndim(mu1) == 0:
+            return Ufull[0].T, its[0][0]
         return Ufull, its[0]
     finally:
         lib = _lib.load()
@@ -104,6 +108,20 @@ def test_ranks_two_groups_of_ctas_nonuniform_mesh_diffusion(oracle):
     Uo, ito = oracle.fom_burgers(X, At, 3, u0, 4.3, 1e-4, 0.017)
     assert np.array_equal(it, ito), (it, ito)
     assert rel_l2_per_step(U, Uo) <= TOL
+
+
+def test_ranks_two_samples_batched_initial_state(oracle):
+    """B = 2 samples one after the other in ONE launch per rank (the epochs run on across the samples), (B, N_local) u0."""
+    N, R = 65536 + 100, 3
+    X = np.linspace(0.0, 100.0, N)
+    At = 0.05 * 511.0 / (N - 1)
+    mu1 = np.array([4.3, 5.4]); mu2 = np.array([0.017, 0.028])
+    u0 = np.stack([np.ones(N), 1.0 + 0.2 * np.sin(X / 7.0)])
+    U, it = _run_ranks(X, At, 8, u0, mu1, 0.0, mu2, R)
+    for b in range(2):
+        Uo, ito = oracle.fom_burgers(X, At, 8, u0[b], mu1[b], 0.0, mu2[b])
+        assert np.array_equal(it[b], ito), (b, it[b], ito)
+        assert rel_l2_per_step(U[b].T, Uo) <= TOL
 
 
 def test_ranks_argument_checks():
