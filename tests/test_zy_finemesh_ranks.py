@@ -124,6 +124,38 @@ def test_ranks_two_samples_batched_initial_state(oracle):
         assert rel_l2_per_step(U[b].T, Uo) <= TOL
 
 
+def test_missing_rank_gives_up_instead_of_hanging():
+    """Only rank 0 of 2 launches: its kernel waits 10 s for rank 1's interface row, raises the failure word and leaves."""
+    import time
+    import torch
+    from burgers_b200 import _lib
+    from burgers_b200.finemesh_dist import PeerExchange, node_partition
+    lib = _lib.load()
+    dev = torch.device("cuda:0")
+    N = 40000
+    X = torch.linspace(0.0, 100.0, N, dtype=torch.float64, device=dev)
+    off, cnt = node_partition(N, 2)[0]
+    ex = PeerExchange.local(2)
+    try:
+        u0 = torch.ones(cnt, dtype=torch.float64, device=dev)
+        m1 = torch.tensor([4.75], dtype=torch.float64, device=dev); m2 = torch.tensor([0.02], dtype=torch.float64, device=dev)
+        U = torch.zeros((1, 5, cnt), dtype=torch.float64, device=dev)
+        ws = torch.empty(int(lib.bx_fine_workspace_bytes(cnt)), dtype=torch.uint8, device=dev)
+        st = torch.cuda.Stream(dev)
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+        _lib.check(lib.bx_fom_picard_finemesh_ranks(1, N, off, cnt, 4, X.data_ptr(), u0.data_ptr(), 0, m1.data_ptr(), m2.data_ptr(),
+                                                    0.05 * 511.0 / (N - 1), 0.0, 1e-6, 20, U.data_ptr(), None, ws.data_ptr(), 2, 0,
+                                                    ex[0].pointer_array(), st.cuda_stream), "bx_fom_picard_finemesh_ranks")
+        assert ex[0].failed(st.cuda_stream)          # synchronises the stream
+        dt = time.perf_counter() - t0
+        assert 8.0 < dt < 40.0, dt
+        assert ex[1].failed(st.cuda_stream)          # the failure word was raised in every rank's buffer
+    finally:
+        for ptr in ex[0].bufs:
+            lib.bx_peer_free(ptr)
+
+
 def test_ranks_argument_checks():
     from burgers_b200 import _lib
     lib = _lib.load()
