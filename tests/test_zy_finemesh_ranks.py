@@ -66,7 +66,7 @@ def _run_ranks(X, At, nsteps, u0, mu1, E, mu2, R, launches=1):
 
 
 @pytest.mark.parametrize("rows", [-1, 16, 8])
-@pytest.mark.parametrize("N,R", [(100003, 2), (100003, 3), (8192 * 5, 5), (131072 + 7, 8)])
+@pytest.mark.parametrize("N,R", [(100003, 1), (100003, 2), (100003, 3), (8192 * 5, 5), (131072 + 7, 8)])
 def test_ranks_vs_oracle_and_single_kernel(N, R, rows, oracle):
     """rows: mesh rows per thread of the kernel instance (-1: automatic = 4 at these sizes)."""
     import burgers_b200
