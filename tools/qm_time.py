@@ -10,6 +10,8 @@ B = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
 proj = sys.argv[2] if len(sys.argv) > 2 else "Galerkin"
 steps = int(sys.argv[3]) if len(sys.argv) > 3 else 500
 n = int(sys.argv[4]) if len(sys.argv) > 4 else 21
+if os.environ.get("QM_GROUP"):
+    burgers_b200.set_tuning("qm_group", int(os.environ["QM_GROUP"]))
 if len(sys.argv) > 5:
     burgers_b200.set_tuning("qm_schedule", int(sys.argv[5]))   # 0 v2 / 1 shared tile / 2 chunked global
 G = os.path.join(os.path.dirname(__file__), "..", "tests", "golden")
