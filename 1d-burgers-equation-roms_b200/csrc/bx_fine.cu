@@ -464,6 +464,17 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
                         double *d = s_grp + 8 * warp;
                         d[0] = a3; d[1] = b3; d[2] = g3; d[3] = r3; d[4] = F3; d[5] = G3; d[6] = R3;
                     }
+                } else if (warp == ng) {
+                    // beside the fold, an idle warp: the rank's norm partials, fixed order (lane l takes CTAs 5 l .. 5 l + 4,
+                    // then a butterfly)
+                    double ra = 0.0, rb = 0.0;
+#pragma unroll
+                    for (int j = 0; j < 5; ++j) {
+                        const int c = 5 * lane + j;
+                        if (c < G) { ra += s_rows[LL_VALUES * c + 7]; rb += s_rows[LL_VALUES * c + 8]; }
+                    }
+                    warp_sum_pair(ra, rb);
+                    if (lane == 0) { s_dec[6] = ra; s_dec[7] = rb; }
                 }
                 __syncthreads();
                 if (warp == 0) {
@@ -473,10 +484,7 @@ template <int FM, bool MULTI> __global__ void __launch_bounds__(FT, 1) fine_fom_
                         a4 = d[0]; b4 = d[1]; g4 = d[2]; r4 = d[3]; F4 = d[4]; G4 = d[5]; R4 = d[6];
                     }
                     const Lvl l2 = group_up<3>(ng, lane, a4, b4, g4, r4, F4, G4, R4);   // -> the rank's row + fgr
-                    // the rank's norm partials, fixed order: lane l takes CTAs 5 l .. 5 l + 4, then a butterfly
-                    double ra = 0.0, rb = 0.0;
-                    for (int c = 5 * lane; c < 5 * lane + 5 && c < G; ++c) { ra += s_rows[LL_VALUES * c + 7]; rb += s_rows[LL_VALUES * c + 8]; }
-                    warp_sum_pair(ra, rb);
+                    const double ra = s_dec[6], rb = s_dec[7];   // (s_dec[6 .. 8] are rewritten below, by this warp)
                     ++xe;
                     double v[PX_VALUES];
                     if (cta == 0) {
