@@ -91,11 +91,14 @@ __device__ __forceinline__ void cp_async8(unsigned int smem_addr, const double *
 
 // BX_FINE_TRACE (experiments, tools/fine_trace.py): cycles of thread 0 of CTA 0 between marks, summed per mark
 #ifdef BX_FINE_TRACE
+#ifndef FINE_TRACE_RANK
+#define FINE_TRACE_RANK 0   // which rank of a partitioned trajectory is traced (clock64 is per SM: one CTA only)
+#endif
 __device__ unsigned long long g_fine_trace[32];
 __device__ unsigned long long g_fine_tlast;
 #define FINE_MARK(i)                                                      \
     do {                                                                  \
-        if (threadIdx.x == 0 && blockIdx.x == 0) {                        \
+        if (threadIdx.x == 0 && blockIdx.x == 0 && p.rank == FINE_TRACE_RANK) { \
             const unsigned long long t_ = clock64();                      \
             g_fine_trace[i] += t_ - g_fine_tlast;                         \
             g_fine_trace[16 + (i)] += 1ull;                               \
